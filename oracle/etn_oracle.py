@@ -1,0 +1,206 @@
+"""ctypes binding for oracle/libetn_oracle.so plus the map-level restatement of
+``truncateEmbeddings`` (reference: core/internal/api/handlers.go:2062-2078).
+
+TEST INFRASTRUCTURE ONLY — see the header of etn_oracle.c.  Imported by tests/,
+``__graft_entry__.smoke()`` and bench.py's cpu_baseline / ``--impl reference`` legs; the
+product package (llm-mcp_b200/) never imports it.  PARITY UNPINNED: the reference holds no
+golden vectors for this path.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "libetn_oracle.so")
+
+F32, F64 = 0, 1
+TRUNCATE, TRUNCATE_RENORM = 0, 1
+_NP = {F32: np.float32, F64: np.float64}
+
+
+def build(force: bool = False) -> str:
+    """Compile the C oracle with gcc (oracle/Makefile)."""
+    src = os.path.join(_HERE, "etn_oracle.c")
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "-s"])
+    return _SO
+
+
+_lib = None
+
+
+def lib() -> ctypes.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_SO):
+            build()
+        L = ctypes.CDLL(_SO)
+        i64, vp, ci = ctypes.c_int64, ctypes.c_void_p, ctypes.c_int
+        L.etn_oracle_fill.argtypes = [ctypes.c_uint64, i64, i64, i64, i64, i64, ci, vp]
+        L.etn_oracle_truncate.argtypes = [i64, i64, i64, ci, vp, vp]
+        L.etn_oracle_renorm_exact.argtypes = [i64, i64, i64, ci, vp, vp]
+        L.etn_oracle_ragged.argtypes = [i64, i64, vp, vp, ci, ci, vp, vp]
+        L.etn_oracle_renorm_go.argtypes = [i64, i64, i64, ci, vp, vp, ci]
+        L.etn_oracle_reslice.argtypes = [i64, i64, vp]
+        L.etn_oracle_reslice.restype = i64
+        L.etn_oracle_max_ulp.argtypes = [i64, ci, vp, vp, ctypes.POINTER(i64)]
+        L.etn_oracle_max_ulp.restype = i64
+        _lib = L
+    return _lib
+
+
+def dtype_code(dt) -> int:
+    dt = np.dtype(dt)
+    if dt == np.float32:
+        return F32
+    if dt == np.float64:
+        return F64
+    raise TypeError(f"unsupported dtype {dt}")
+
+
+def _ptr(a: np.ndarray) -> ctypes.c_void_p:
+    return ctypes.c_void_p(a.ctypes.data)
+
+
+def _check(rc: int, what: str) -> None:
+    if rc < 0:
+        raise ValueError(f"{what}: oracle error {rc}")
+
+
+def fill(seed: int, rows: int, D: int, dtype, row0: int = 0, ncols: int | None = None) -> np.ndarray:
+    """Synthetic matrix of SURVEY.md §8(d): rows [row0, row0+rows) x cols [0, ncols)."""
+    ncols = D if ncols is None else ncols
+    out = np.empty((rows, ncols), dtype=dtype)
+    _check(lib().etn_oracle_fill(seed, row0, rows, D, ncols, ncols, dtype_code(dtype), _ptr(out)), "fill")
+    return out
+
+
+def fill_numpy(seed: int, rows: int, D: int, dtype, row0: int = 0, ncols: int | None = None) -> np.ndarray:
+    """Same generator in numpy integer arithmetic (cross-check of the C one)."""
+    ncols = D if ncols is None else ncols
+    r = np.arange(row0, row0 + rows, dtype=np.uint64)[:, None]
+    c = np.arange(ncols, dtype=np.uint64)[None, :]
+    with np.errstate(over="ignore"):
+        z = np.uint64(seed) ^ (r * np.uint64(D) + c)
+        z = z + np.uint64(0x9E3779B97F4A7C15)
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        z = z ^ (z >> np.uint64(31))
+    v = ((z >> np.uint64(32)).astype(np.uint32).view(np.int32) >> 8).astype(np.float64) * 2.0 ** -28
+    return v.astype(dtype)
+
+
+def truncate(x: np.ndarray, k: int) -> np.ndarray:
+    x = np.ascontiguousarray(x)
+    batch, D = x.shape
+    out = np.empty((batch, min(k, D)), dtype=x.dtype)
+    _check(lib().etn_oracle_truncate(batch, D, k, dtype_code(x.dtype), _ptr(x), _ptr(out)), "truncate")
+    return out
+
+
+def renorm_exact(x: np.ndarray, k: int) -> np.ndarray:
+    x = np.ascontiguousarray(x)
+    batch, D = x.shape
+    out = np.empty((batch, min(k, D)), dtype=x.dtype)
+    _check(lib().etn_oracle_renorm_exact(batch, D, k, dtype_code(x.dtype), _ptr(x), _ptr(out)), "renorm_exact")
+    return out
+
+
+def renorm_go(x: np.ndarray, k: int, nthreads: int = 1, out: np.ndarray | None = None) -> np.ndarray:
+    x = np.ascontiguousarray(x)
+    batch, D = x.shape
+    if out is None:
+        out = np.empty((batch, min(k, D)), dtype=x.dtype)
+    _check(lib().etn_oracle_renorm_go(batch, D, k, dtype_code(x.dtype), _ptr(x), _ptr(out), nthreads), "renorm_go")
+    return out
+
+
+def ragged_offsets(k_per_row: np.ndarray, D: int) -> np.ndarray:
+    """Exclusive prefix sum of min(k, D): CSR element offsets, length batch+1."""
+    kk = np.minimum(np.asarray(k_per_row, dtype=np.int64), D)
+    off = np.zeros(len(kk) + 1, dtype=np.int64)
+    np.cumsum(kk, out=off[1:])
+    return off
+
+
+def ragged(x: np.ndarray, k_per_row: np.ndarray, mode: int) -> tuple[np.ndarray, np.ndarray]:
+    x = np.ascontiguousarray(x)
+    batch, D = x.shape
+    kpr = np.ascontiguousarray(k_per_row, dtype=np.int32)
+    off = ragged_offsets(kpr, D)
+    out = np.empty(int(off[-1]), dtype=x.dtype)
+    _check(lib().etn_oracle_ragged(batch, D, _ptr(kpr), _ptr(off), dtype_code(x.dtype), mode, _ptr(x), _ptr(out)), "ragged")
+    return out, off
+
+
+def max_ulp(a: np.ndarray, b: np.ndarray) -> tuple[int, int]:
+    """(largest ulp distance, flat index); distance -1 means a NaN was seen."""
+    a = np.ascontiguousarray(a)
+    b = np.ascontiguousarray(b)
+    assert a.dtype == b.dtype and a.size == b.size, (a.dtype, b.dtype, a.shape, b.shape)
+    arg = ctypes.c_int64(0)
+    d = lib().etn_oracle_max_ulp(a.size, dtype_code(a.dtype), _ptr(a), _ptr(b), ctypes.byref(arg))
+    return int(d), int(arg.value)
+
+
+def reslice(lens: np.ndarray, dims: int) -> int:
+    lens = np.ascontiguousarray(lens, dtype=np.int64)
+    return int(lib().etn_oracle_reslice(len(lens), dims, _ptr(lens)))
+
+
+# ---------------------------------------------------------------------------
+# Map-level restatement of the reference function (pure Python; small cases only)
+# ---------------------------------------------------------------------------
+
+def truncate_embeddings_ref(result, dims: int) -> None:
+    """``truncateEmbeddings(result map[string]any, dims int)`` — handlers.go:2062-2078.
+
+    JSON model: object → dict, array → list, number → float.  Mutates ``result`` in place:
+      :2064-2067  ``data`` missing or not an array → no-op
+      :2069-2072  items that are not objects are skipped
+      :2073       ``embedding`` that is not an array (base64 string, null) is left alone
+      :2074       only vectors with len > dims are cut; shorter ones are never padded
+      :2075       keep the first ``dims`` components, same order, same values
+    Nothing is renormalised.
+    """
+    if not isinstance(result, dict):
+        return
+    data = result.get("data")
+    if not isinstance(data, list):
+        return
+    for item in data:
+        if not isinstance(item, dict):
+            continue
+        emb = item.get("embedding")
+        if isinstance(emb, list) and len(emb) > dims:
+            item["embedding"] = emb[:dims]
+
+
+def resolve_dims(req_dimensions: int, env: dict | None = None) -> int:
+    """handlers.go:1874-1877 + config.go:17-24: request value, else CLOUD_EMBED_DIMENSIONS
+    (unset, empty or unparsable → 0).  The op runs only when the result is > 0 (:1891)."""
+    env = os.environ if env is None else env
+    dims = req_dimensions
+    if dims == 0:
+        v = env.get("CLOUD_EMBED_DIMENSIONS", "")
+        if v != "":
+            try:
+                dims = _go_atoi(v)
+            except ValueError:
+                dims = 0
+    return dims
+
+
+def _go_atoi(s: str) -> int:
+    """strconv.Atoi: optional sign then decimal digits only (no spaces, no underscores)."""
+    body = s[1:] if s[:1] in "+-" else s
+    if not body or not body.isascii() or not body.isdigit():
+        raise ValueError(s)
+    n = int(s)
+    if not -(1 << 63) <= n < (1 << 63):
+        raise ValueError(s)
+    return n
