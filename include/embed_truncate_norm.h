@@ -1,0 +1,142 @@
+/*
+ * embed_truncate_norm.h — C-ABI of libembed_truncate_norm.so (CUDA, sm_100a / B200).
+ *
+ * One op: Matryoshka truncation of embedding vectors, optionally followed by L2
+ * renormalisation, batched and device-resident.  It replaces the per-vector loop of
+ *     truncateEmbeddings(result map[string]any, dims int)
+ *         /root/reference/core/internal/api/handlers.go:2062-2078
+ * called from Server.HandleEmbeddings at handlers.go:1891-1893 when dims > 0.
+ *
+ * The reference has no FFI boundary (CGO_ENABLED=0, one private function,
+ * one call site), so every entry point below is the function a new cgo package
+ * `core/internal/embedgpu` would bind; INTEGRATION.md shows that binding.  The reference
+ * interface each one stands in for is cited per function.
+ *
+ * Conventions
+ *   - Matrices are row-major.  `in` is [batch x D]; dense `out` is [batch x kk] with
+ *     kk = min(k, D) (handlers.go:2074: vectors with len <= dims are left whole, never
+ *     padded).  Components keep their order; TRUNCATE keeps their bits.
+ *   - dtype: ETN_F32 = IEEE binary32, ETN_F64 = IEEE binary64 (the reference's element
+ *     type: encoding/json decodes into float64, handlers.go:2047-2050).  Little endian.
+ *   - mode:  ETN_TRUNCATE        out = in[:, :kk]                       (the reference)
+ *            ETN_TRUNCATE_RENORM out = in[:, :kk] / ||in[:, :kk]||_2    (BASELINE.json;
+ *            not in the reference).  A row whose prefix is all zeros is
+ *            copied unchanged; finite input always gives finite output (Go's encoder
+ *            drops the whole body on NaN/Inf, helpers.go:13-14).  Results are within
+ *            2 ulp of the exactly rounded quotient for every finite input, subnormals and
+ *            values whose squares overflow included.
+ *   - Return value: 0 = ok; negative = ETN_ERR_* argument errors; positive = the
+ *     cudaError_t reported by the CUDA runtime.  Nothing aborts, throws or prints.
+ *   - Device entry points work on the calling thread's current CUDA device and enqueue
+ *     on `stream` (a cudaStream_t; NULL = the legacy default stream) without
+ *     synchronising.  They allocate nothing and keep no pointer.
+ *   - `in` and `out` must not overlap, except out == in with k >= D (normalise in place).
+ *   - Every entry point is re-entrant and may be called from any OS thread (Go handlers
+ *     run on arbitrary threads).
+ */
+#ifndef EMBED_TRUNCATE_NORM_H_
+#define EMBED_TRUNCATE_NORM_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define ETN_API __attribute__((visibility("default")))
+#else
+#define ETN_API
+#endif
+
+#define ETN_VERSION 100 /* 0.1.0 */
+
+#define ETN_F32 0
+#define ETN_F64 1
+
+#define ETN_TRUNCATE 0
+#define ETN_TRUNCATE_RENORM 1
+
+#define ETN_OK 0
+#define ETN_ERR_NULL (-1)     /* a required pointer is NULL */
+#define ETN_ERR_SHAPE (-2)    /* batch < 0, D <= 0, k <= 0, bad pitch or offsets */
+#define ETN_ERR_ENUM (-3)     /* unknown dtype or mode */
+#define ETN_ERR_ALIGN (-4)    /* pointer not aligned to the element size */
+#define ETN_ERR_NOT_INIT (-5) /* host path used before etn_init */
+#define ETN_ERR_DEVICE (-6)   /* bad device list / n_devices */
+
+/* Library version (ETN_VERSION of the build).  No reference counterpart. */
+ETN_API int etn_version(void);
+
+/* Text for any code returned by this library (static storage; cudaGetErrorString for
+ * positive codes).  Stands in for the err.Error() strings the handler logs with
+ * slog.Error (handlers.go:1882). */
+ETN_API const char *etn_strerror(int code);
+
+/* The op, device-resident — north_star signature.  TRUNCATE_RENORM of the first k of D
+ * components of each of `batch` rows.  Replaces the loop body handlers.go:2068-2076 for a
+ * whole packed response at once.  k >= D is legal (normalise whole rows). */
+ETN_API int embed_truncate_norm(int64_t batch, int64_t D, int64_t k, int dtype, const void *in,
+                        void *out, void *stream);
+
+/* Same shape contract, ETN_TRUNCATE only: bit-exact with the reference's
+ * m["embedding"] = emb[:dims] (handlers.go:2075) on the packed matrix. */
+ETN_API int embed_truncate(int64_t batch, int64_t D, int64_t k, int dtype, const void *in, void *out,
+                   void *stream);
+
+/* Ragged batch: row r keeps kr = min(k_per_row[r], D) components, written at element
+ * offset out_offsets[r] of the packed output (CSR style; out_offsets has `batch` entries,
+ * device memory, as has k_per_row).  One response may mix vector lengths — each vector is
+ * handled on its own at handlers.go:2068-2076 — and one launch may carry many requests
+ * with different `dimensions` (handlers.go:1874-1877). */
+ETN_API int embed_truncate_norm_ragged(int64_t batch, int64_t D, const int32_t *k_per_row,
+                               const int64_t *out_offsets, int dtype, int mode, const void *in,
+                               void *out, void *stream);
+
+/* ---- host path: what the handler calls between proxyOpenAIEmbed (handlers.go:1879) and
+ * WriteJSON (handlers.go:1894) once the response vectors are packed in host memory. ---- */
+
+/* Creates per-device streams, events and staging buffers.  device_ids == NULL or
+ * n_devices == 0 selects every visible device.  Call once from main (the reference wires
+ * its components at core/cmd/core/main.go:49-51).  Calling it again is a no-op. */
+ETN_API int etn_init(const int *device_ids, int n_devices);
+
+/* Releases what etn_init created (main.go:118-122, graceful shutdown). */
+ETN_API void etn_shutdown(void);
+
+/* Number of devices etn_init bound (0 before init).  No reference counterpart (the
+ * reference never enumerates GPUs; its device table is Ollama hosts, router.go:286-322). */
+ETN_API int etn_device_count(void);
+
+/* Page-locked host memory for the packed request/response buffers (never Go memory, so
+ * no Go pointer is retained by C and async DMA is legal).  NULL on failure.  Takes the place
+ * of the []any backing arrays json.Decode allocates at handlers.go:2047-2050. */
+ETN_API void *etn_alloc_pinned(size_t bytes);
+ETN_API void etn_free_pinned(void *p);
+
+/* End to end on host buffers, synchronous — the call that replaces
+ * truncateEmbeddings(result, dims) at handlers.go:1891-1893: rows are split into contiguous blocks over the
+ * first n_devices devices of etn_init (0 = all of them), each block is copied prefix-only
+ * (kk of D columns) to its device in chunks, processed and copied back, with the copies
+ * of one chunk overlapping the kernel of another.  host_in is [batch x D] with a row
+ * pitch of in_pitch_bytes (>= D * elem size, or 0 for dense); host_out is dense
+ * [batch x kk].  Pinned buffers (etn_alloc_pinned) give full PCIe speed; pageable memory
+ * works but is slower.  No collective is involved: rows are independent. */
+ETN_API int embed_truncate_norm_host(int64_t batch, int64_t D, int64_t k, int dtype, int mode,
+                             const void *host_in, int64_t in_pitch_bytes, void *host_out,
+                             int n_devices);
+
+/* ---- bench/test utility ---- */
+
+/* Writes the synthetic matrix of SURVEY.md §8(d) (as amended in DESIGN.md: signed 24-bit
+ * integers * 2^-28) for rows [row0, row0+rows) x cols [0, ncols) of a logical
+ * [.. x D] matrix into device memory with leading dimension ld.  No reference
+ * counterpart (the reference has no benchmark for this path). */
+ETN_API int etn_fill_synthetic(uint64_t seed, int64_t row0, int64_t rows, int64_t D, int64_t ncols,
+                       int64_t ld, int dtype, void *dev_out, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EMBED_TRUNCATE_NORM_H_ */

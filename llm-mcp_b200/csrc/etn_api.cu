@@ -1,0 +1,378 @@
+// etn_api.cu — the C-ABI of libembed_truncate_norm.so (declared in
+// include/embed_truncate_norm.h) and the host side above the kernels: argument checks,
+// kernel selection, and the end-to-end host-buffer path (chunked prefix-only H2D, kernel,
+// D2H, row-sharded over devices with one host thread and its own streams per device).
+//
+// Reference behaviour being replaced: truncateEmbeddings, core/internal/api/handlers.go:2062-2078,
+// called at handlers.go:1891-1893.  No torch, no NCCL, no CPU compute fallback: if the
+// CUDA runtime reports an error the caller gets its code.
+#include "../../include/embed_truncate_norm.h"
+#include "etn_kernels.cuh"
+
+#include <algorithm>
+#include <atomic>
+#include <mutex>
+#include <thread>
+#include <vector>
+
+namespace {
+
+using namespace etn;
+
+inline bool aligned_to(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
+
+// ------------------------------------------------------------ device info ----
+struct DeviceInfo {
+  std::atomic<int> sms{0};
+};
+constexpr int kMaxDevices = 64;
+DeviceInfo g_info[kMaxDevices];
+
+int sm_count(int dev, int* out) {
+  if (dev < 0 || dev >= kMaxDevices) { *out = 148; return 0; }
+  int v = g_info[dev].sms.load(std::memory_order_relaxed);
+  if (v == 0) {
+    cudaError_t e = cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+    if (e != cudaSuccess) return (int)e;
+    g_info[dev].sms.store(v, std::memory_order_relaxed);
+  }
+  *out = v;
+  return 0;
+}
+
+// Persistent grid: one full wave of resident blocks, or fewer if the batch is small.
+template <typename K>
+int grid_for(K kernel, int64_t blocks_needed, int* grid) {
+  int dev = 0, sms = 0, per_sm = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (int rc = sm_count(dev, &sms)) return rc;
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, 0);
+  if (e != cudaSuccess) return (int)e;
+  if (per_sm < 1) per_sm = 1;
+  const int64_t cap = (int64_t)sms * per_sm;
+  *grid = (int)std::max<int64_t>(1, std::min<int64_t>(blocks_needed, cap));
+  return 0;
+}
+
+// ------------------------------------------------------------- launchers ----
+// MINB = resident blocks per SM the register allocation is held to (bytes in flight per SM
+// = MINB * 8 warps * R*NV * 512 B).
+template <typename T, int NV, int R, int MODE, int MINB>
+int launch_reg(const void* in, void* out, int64_t batch, int64_t in_pitch, int nvec, cudaStream_t s) {
+  auto kern = rows_reg_kernel<T, NV, R, MODE, MINB>;
+  int grid = 0;
+  const int64_t rows_per_block = (int64_t)kWarpsPerBlock * R;
+  if (int rc = grid_for(kern, (batch + rows_per_block - 1) / rows_per_block, &grid)) return rc;
+  kern<<<grid, kThreads, 0, s>>>((const char*)in, (char*)out, batch, in_pitch, nvec);
+  return (int)cudaGetLastError();
+}
+
+template <typename T, int MODE>
+int launch_general(const void* in, void* out, int64_t batch, int64_t D, int64_t k,
+                   const int32_t* k_per_row, const int64_t* out_offsets, cudaStream_t s) {
+  auto kern = rows_general_kernel<T, MODE>;
+  int grid = 0;
+  if (int rc = grid_for(kern, (batch + kWarpsPerBlock - 1) / kWarpsPerBlock, &grid)) return rc;
+  kern<<<grid, kThreads, 0, s>>>((const T*)in, (T*)out, batch, D, k, k_per_row, out_offsets);
+  return (int)cudaGetLastError();
+}
+
+// Dense rows: the register-row kernel when both sides are 16-byte tileable and the prefix
+// fits 16 vectors per lane (8 KiB per row); the general kernel otherwise.
+template <typename T, int MODE>
+int launch_dense(const void* in, void* out, int64_t batch, int64_t D, int64_t kk, cudaStream_t s) {
+  const int64_t in_pitch = D * (int64_t)sizeof(T);
+  const int64_t k_bytes = kk * (int64_t)sizeof(T);
+  const bool tileable = aligned_to(in, 16) && aligned_to(out, 16) && in_pitch % 16 == 0 &&
+                        k_bytes % 16 == 0;
+  if (tileable && k_bytes <= 16 * 512) {
+    const int nvec = (int)(k_bytes / 16);
+    const int nv = (nvec + 31) / 32;
+    // Truncation moves bytes; one instantiation (T = float) serves both element types.
+    using TT = typename std::conditional<MODE == kModeTruncate, float, T>::type;
+    constexpr int MB = MODE == kModeTruncate ? 4 : (sizeof(T) == 4 ? 4 : 2);
+    constexpr int MB16 = (MODE == kModeRenorm && sizeof(T) == 8) ? 1 : 2;
+    if (nv <= 1)  return launch_reg<TT, 1, 8, MODE, MB>(in, out, batch, in_pitch, nvec, s);
+    if (nv <= 2)  return launch_reg<TT, 2, 4, MODE, MB>(in, out, batch, in_pitch, nvec, s);
+    if (nv <= 4)  return launch_reg<TT, 4, 2, MODE, MB>(in, out, batch, in_pitch, nvec, s);
+    if (nv <= 8)  return launch_reg<TT, 8, 1, MODE, MB>(in, out, batch, in_pitch, nvec, s);
+    return launch_reg<TT, 16, 1, MODE, MB16>(in, out, batch, in_pitch, nvec, s);
+  }
+  return launch_general<T, MODE>(in, out, batch, D, kk, nullptr, nullptr, s);
+}
+
+int check_dense(int64_t batch, int64_t D, int64_t k, int dtype, const void* in, const void* out) {
+  if (dtype != ETN_F32 && dtype != ETN_F64) return ETN_ERR_ENUM;
+  if (batch < 0 || D <= 0 || k <= 0) return ETN_ERR_SHAPE;
+  if (batch == 0) return ETN_OK;
+  if (!in || !out) return ETN_ERR_NULL;
+  const size_t es = dtype == ETN_F32 ? 4 : 8;
+  if (!aligned_to(in, es) || !aligned_to(out, es)) return ETN_ERR_ALIGN;
+  return ETN_OK;
+}
+
+int run_dense(int64_t batch, int64_t D, int64_t k, int dtype, int mode, const void* in, void* out,
+              cudaStream_t s) {
+  const int64_t kk = std::min(k, D);
+  if (mode == ETN_TRUNCATE) {
+    return dtype == ETN_F32 ? launch_dense<float, kModeTruncate>(in, out, batch, D, kk, s)
+                            : launch_dense<double, kModeTruncate>(in, out, batch, D, kk, s);
+  }
+  return dtype == ETN_F32 ? launch_dense<float, kModeRenorm>(in, out, batch, D, kk, s)
+                          : launch_dense<double, kModeRenorm>(in, out, batch, D, kk, s);
+}
+
+// --------------------------------------------------------------- host path ----
+constexpr int kSlots = 3;                          // chunks in flight per device
+constexpr size_t kSlotBytes = 32u << 20;           // staging per slot (prefix bytes)
+
+struct DevCtx {
+  int dev = -1;
+  cudaStream_t stream[kSlots] = {};
+  void* stage[kSlots] = {};
+  std::mutex mu;                                   // one host call at a time per device
+};
+
+std::mutex g_init_mu;
+std::vector<DevCtx*> g_ctx;                        // guarded by g_init_mu for (de)construction
+std::atomic<int> g_ndev{0};
+
+void destroy_ctx(DevCtx* c) {
+  if (!c) return;
+  if (cudaSetDevice(c->dev) == cudaSuccess) {
+    for (int i = 0; i < kSlots; ++i) {
+      if (c->stream[i]) { cudaStreamSynchronize(c->stream[i]); cudaStreamDestroy(c->stream[i]); }
+      if (c->stage[i]) cudaFree(c->stage[i]);
+    }
+  }
+  delete c;
+}
+
+// Processes rows [0, rows) of one device's block.  host_in/host_out already point at the
+// block.  Every chunk runs H2D -> kernel (in place on the dense staging tile) -> D2H on its
+// slot's stream; the three slots keep both copy engines and the SMs busy at once.
+int run_block(DevCtx* c, int64_t rows, int64_t D, int64_t kk, int dtype, int mode,
+              const char* host_in, int64_t in_pitch, char* host_out) {
+  std::lock_guard<std::mutex> lock(c->mu);
+  cudaError_t e = cudaSetDevice(c->dev);
+  if (e != cudaSuccess) return (int)e;
+  const int64_t es = dtype == ETN_F32 ? 4 : 8;
+  const int64_t k_bytes = kk * es;
+  int64_t chunk_rows = (int64_t)(kSlotBytes / (size_t)k_bytes);
+  if (chunk_rows < 1) return ETN_ERR_SHAPE;        // one row prefix larger than a slot
+  int rc = 0;
+  int64_t done = 0;
+  for (int64_t ci = 0; done < rows && rc == 0; ++ci) {
+    const int slot = (int)(ci % kSlots);
+    cudaStream_t s = c->stream[slot];
+    const int64_t n = std::min(chunk_rows, rows - done);
+    const char* src = host_in + done * in_pitch;
+    if (in_pitch == k_bytes) {
+      e = cudaMemcpyAsync(c->stage[slot], src, (size_t)(n * k_bytes), cudaMemcpyHostToDevice, s);
+    } else {
+      e = cudaMemcpy2DAsync(c->stage[slot], (size_t)k_bytes, src, (size_t)in_pitch, (size_t)k_bytes,
+                            (size_t)n, cudaMemcpyHostToDevice, s);
+    }
+    if (e != cudaSuccess) { rc = (int)e; break; }
+    // staging is dense [n x kk]: D == kk, so renormalising in place is allowed
+    if (mode == ETN_TRUNCATE_RENORM) {
+      rc = run_dense(n, kk, kk, dtype, mode, c->stage[slot], c->stage[slot], s);
+      if (rc) break;
+    }
+    e = cudaMemcpyAsync(host_out + done * k_bytes, c->stage[slot], (size_t)(n * k_bytes),
+                        cudaMemcpyDeviceToHost, s);
+    if (e != cudaSuccess) { rc = (int)e; break; }
+    done += n;
+  }
+  for (int i = 0; i < kSlots; ++i) {
+    e = cudaStreamSynchronize(c->stream[i]);
+    if (e != cudaSuccess && rc == 0) rc = (int)e;
+  }
+  return rc;
+}
+
+}  // namespace
+
+// =============================================================== C-ABI ======
+extern "C" {
+
+int etn_version(void) { return ETN_VERSION; }
+
+const char* etn_strerror(int code) {
+  switch (code) {
+    case ETN_OK: return "ok";
+    case ETN_ERR_NULL: return "null pointer";
+    case ETN_ERR_SHAPE: return "bad shape (batch < 0, D <= 0, k <= 0, bad pitch or offsets)";
+    case ETN_ERR_ENUM: return "unknown dtype or mode";
+    case ETN_ERR_ALIGN: return "pointer not aligned to the element size";
+    case ETN_ERR_NOT_INIT: return "etn_init has not been called";
+    case ETN_ERR_DEVICE: return "bad device list";
+    default: break;
+  }
+  if (code > 0) return cudaGetErrorString((cudaError_t)code);
+  return "unknown error";
+}
+
+int embed_truncate_norm(int64_t batch, int64_t D, int64_t k, int dtype, const void* in, void* out,
+                        void* stream) {
+  if (int rc = check_dense(batch, D, k, dtype, in, out)) return rc;
+  if (batch == 0) return ETN_OK;
+  return run_dense(batch, D, k, dtype, ETN_TRUNCATE_RENORM, in, out, (cudaStream_t)stream);
+}
+
+int embed_truncate(int64_t batch, int64_t D, int64_t k, int dtype, const void* in, void* out,
+                   void* stream) {
+  if (int rc = check_dense(batch, D, k, dtype, in, out)) return rc;
+  if (batch == 0) return ETN_OK;
+  return run_dense(batch, D, k, dtype, ETN_TRUNCATE, in, out, (cudaStream_t)stream);
+}
+
+int embed_truncate_norm_ragged(int64_t batch, int64_t D, const int32_t* k_per_row,
+                               const int64_t* out_offsets, int dtype, int mode, const void* in,
+                               void* out, void* stream) {
+  if ((dtype != ETN_F32 && dtype != ETN_F64) || (mode != ETN_TRUNCATE && mode != ETN_TRUNCATE_RENORM))
+    return ETN_ERR_ENUM;
+  if (batch < 0 || D <= 0) return ETN_ERR_SHAPE;
+  if (batch == 0) return ETN_OK;
+  if (!in || !out || !k_per_row || !out_offsets) return ETN_ERR_NULL;
+  const size_t es = dtype == ETN_F32 ? 4 : 8;
+  if (!aligned_to(in, es) || !aligned_to(out, es) || !aligned_to(k_per_row, 4) ||
+      !aligned_to(out_offsets, 8))
+    return ETN_ERR_ALIGN;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (mode == ETN_TRUNCATE)
+    return dtype == ETN_F32
+               ? launch_general<float, kModeTruncate>(in, out, batch, D, 0, k_per_row, out_offsets, s)
+               : launch_general<double, kModeTruncate>(in, out, batch, D, 0, k_per_row, out_offsets, s);
+  return dtype == ETN_F32
+             ? launch_general<float, kModeRenorm>(in, out, batch, D, 0, k_per_row, out_offsets, s)
+             : launch_general<double, kModeRenorm>(in, out, batch, D, 0, k_per_row, out_offsets, s);
+}
+
+int etn_init(const int* device_ids, int n_devices) {
+  std::lock_guard<std::mutex> lock(g_init_mu);
+  if (!g_ctx.empty()) return ETN_OK;
+  int visible = 0;
+  cudaError_t e = cudaGetDeviceCount(&visible);
+  if (e != cudaSuccess) return (int)e;
+  std::vector<int> ids;
+  if (!device_ids || n_devices <= 0) {
+    for (int i = 0; i < visible; ++i) ids.push_back(i);
+  } else {
+    for (int i = 0; i < n_devices; ++i) {
+      if (device_ids[i] < 0 || device_ids[i] >= visible) return ETN_ERR_DEVICE;
+      ids.push_back(device_ids[i]);
+    }
+  }
+  if (ids.empty()) return ETN_ERR_DEVICE;
+  int prev = 0;
+  cudaGetDevice(&prev);
+  std::vector<DevCtx*> made;
+  int rc = 0;
+  for (int id : ids) {
+    DevCtx* c = new DevCtx();
+    c->dev = id;
+    made.push_back(c);
+    if ((e = cudaSetDevice(id)) != cudaSuccess) { rc = (int)e; break; }
+    for (int i = 0; i < kSlots && rc == 0; ++i) {
+      if ((e = cudaStreamCreateWithFlags(&c->stream[i], cudaStreamNonBlocking)) != cudaSuccess) rc = (int)e;
+      else if ((e = cudaMalloc(&c->stage[i], kSlotBytes)) != cudaSuccess) rc = (int)e;
+    }
+    if (rc) break;
+  }
+  cudaSetDevice(prev);
+  if (rc) { for (DevCtx* c : made) destroy_ctx(c); return rc; }
+  g_ctx.swap(made);
+  g_ndev.store((int)g_ctx.size());
+  return ETN_OK;
+}
+
+void etn_shutdown(void) {
+  std::lock_guard<std::mutex> lock(g_init_mu);
+  int prev = 0;
+  const bool have_prev = cudaGetDevice(&prev) == cudaSuccess;
+  for (DevCtx* c : g_ctx) destroy_ctx(c);
+  g_ctx.clear();
+  g_ndev.store(0);
+  if (have_prev) cudaSetDevice(prev);
+}
+
+int etn_device_count(void) { return g_ndev.load(); }
+
+void* etn_alloc_pinned(size_t bytes) {
+  void* p = nullptr;
+  if (bytes == 0) return nullptr;
+  if (cudaHostAlloc(&p, bytes, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+  return p;
+}
+
+void etn_free_pinned(void* p) {
+  if (p) cudaFreeHost(p);
+}
+
+int embed_truncate_norm_host(int64_t batch, int64_t D, int64_t k, int dtype, int mode,
+                             const void* host_in, int64_t in_pitch_bytes, void* host_out,
+                             int n_devices) {
+  if ((dtype != ETN_F32 && dtype != ETN_F64) || (mode != ETN_TRUNCATE && mode != ETN_TRUNCATE_RENORM))
+    return ETN_ERR_ENUM;
+  if (batch < 0 || D <= 0 || k <= 0) return ETN_ERR_SHAPE;
+  const int64_t es = dtype == ETN_F32 ? 4 : 8;
+  if (in_pitch_bytes == 0) in_pitch_bytes = D * es;
+  if (in_pitch_bytes < D * es || in_pitch_bytes % es != 0) return ETN_ERR_SHAPE;
+  if (n_devices < 0) return ETN_ERR_DEVICE;
+  if (batch == 0) return ETN_OK;
+  if (!host_in || !host_out) return ETN_ERR_NULL;
+  if (!aligned_to(host_in, (size_t)es) || !aligned_to(host_out, (size_t)es)) return ETN_ERR_ALIGN;
+
+  std::vector<DevCtx*> ctx;
+  {
+    std::lock_guard<std::mutex> lock(g_init_mu);
+    ctx = g_ctx;
+  }
+  if (ctx.empty()) return ETN_ERR_NOT_INIT;
+  if (n_devices == 0) n_devices = (int)ctx.size();
+  if (n_devices > (int)ctx.size()) return ETN_ERR_DEVICE;
+  n_devices = (int)std::min<int64_t>(n_devices, batch);
+
+  const int64_t kk = std::min(k, D);
+  const char* hin = (const char*)host_in;
+  char* hout = (char*)host_out;
+  // contiguous row blocks: device g gets rows [g*per, min(batch, (g+1)*per))
+  const int64_t per = (batch + n_devices - 1) / n_devices;
+  int prev = 0;
+  const bool have_prev = cudaGetDevice(&prev) == cudaSuccess;
+  std::vector<int> rcs(n_devices, 0);
+  auto work = [&](int g) {
+    const int64_t r0 = (int64_t)g * per, r1 = std::min(batch, r0 + per);
+    if (r1 <= r0) return;
+    rcs[g] = run_block(ctx[g], r1 - r0, D, kk, dtype, mode, hin + r0 * in_pitch_bytes,
+                       in_pitch_bytes, hout + r0 * kk * es);
+  };
+  if (n_devices == 1) {
+    work(0);
+  } else {
+    std::vector<std::thread> th;
+    for (int g = 0; g < n_devices; ++g) th.emplace_back(work, g);
+    for (auto& t : th) t.join();
+  }
+  if (have_prev) cudaSetDevice(prev);
+  for (int rc : rcs) if (rc) return rc;
+  return ETN_OK;
+}
+
+int etn_fill_synthetic(uint64_t seed, int64_t row0, int64_t rows, int64_t D, int64_t ncols,
+                       int64_t ld, int dtype, void* dev_out, void* stream) {
+  if (dtype != ETN_F32 && dtype != ETN_F64) return ETN_ERR_ENUM;
+  if (rows < 0 || D <= 0 || ncols < 0 || ncols > D || ld < ncols) return ETN_ERR_SHAPE;
+  if (rows == 0 || ncols == 0) return ETN_OK;
+  if (!dev_out) return ETN_ERR_NULL;
+  const int64_t total = rows * ncols;
+  const int grid = (int)std::min<int64_t>((total + 255) / 256, 148 * 16);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (dtype == ETN_F32) fill_kernel<float><<<grid, 256, 0, s>>>((float*)dev_out, seed, row0, rows, D, ncols, ld);
+  else fill_kernel<double><<<grid, 256, 0, s>>>((double*)dev_out, seed, row0, rows, D, ncols, ld);
+  return (int)cudaGetLastError();
+}
+
+}  // extern "C"

@@ -1,0 +1,238 @@
+"""embedgpu — host side above the C-ABI of libembed_truncate_norm.so.
+
+This module mirrors, name for name, the Go package ``core/internal/embedgpu`` proposed in
+INTEGRATION.md (source under ``llm-mcp_b200/go/embedgpu``; the image has no Go toolchain,
+so the Python mirror is what the tests and the bench drive).  Its public surface follows the
+reference call site:
+
+    truncate_embeddings(result, dims)   <->  truncateEmbeddings(result, dims)
+                                             core/internal/api/handlers.go:2062-2078
+    resolve_dims(req_dimensions)        <->  handlers.go:1874-1877 + config.GetenvInt
+                                             (core/internal/config/config.go:17-24)
+
+The computation runs only on the GPU.  If the shared library is missing this module raises
+on first use; there is no CPU path here (the CPU restatement lives in oracle/ and is test
+infrastructure only).
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from typing import Any
+
+import numpy as np
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "libembed_truncate_norm.so")
+
+F32, F64 = 0, 1
+TRUNCATE, TRUNCATE_RENORM = 0, 1
+ERR_NULL, ERR_SHAPE, ERR_ENUM, ERR_ALIGN, ERR_NOT_INIT, ERR_DEVICE = -1, -2, -3, -4, -5, -6
+
+EXPORTS = (
+    "etn_version", "etn_strerror", "embed_truncate_norm", "embed_truncate",
+    "embed_truncate_norm_ragged", "etn_init", "etn_shutdown", "etn_device_count",
+    "etn_alloc_pinned", "etn_free_pinned", "embed_truncate_norm_host", "etn_fill_synthetic",
+)
+
+
+class EtnError(RuntimeError):
+    def __init__(self, code: int, text: str, where: str):
+        super().__init__(f"{where}: {text} (code {code})")
+        self.code = code
+
+
+_lib = None
+
+
+def lib() -> ctypes.CDLL:
+    """Loads libembed_truncate_norm.so (built by __graft_entry__.build / csrc/Makefile)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise FileNotFoundError(
+                f"{LIB_PATH} is missing: build it with `make -C llm-mcp_b200/csrc` "
+                "(nvcc, sm_100a). There is no CPU fallback.")
+        L = ctypes.CDLL(LIB_PATH)
+        i64, vp, ci = ctypes.c_int64, ctypes.c_void_p, ctypes.c_int
+        L.etn_version.restype = ci
+        L.etn_strerror.argtypes = [ci]
+        L.etn_strerror.restype = ctypes.c_char_p
+        L.embed_truncate_norm.argtypes = [i64, i64, i64, ci, vp, vp, vp]
+        L.embed_truncate.argtypes = [i64, i64, i64, ci, vp, vp, vp]
+        L.embed_truncate_norm_ragged.argtypes = [i64, i64, vp, vp, ci, ci, vp, vp, vp]
+        L.etn_init.argtypes = [ctypes.POINTER(ci), ci]
+        L.etn_shutdown.restype = None
+        L.etn_device_count.restype = ci
+        L.etn_alloc_pinned.argtypes = [ctypes.c_size_t]
+        L.etn_alloc_pinned.restype = vp
+        L.etn_free_pinned.argtypes = [vp]
+        L.etn_free_pinned.restype = None
+        L.embed_truncate_norm_host.argtypes = [i64, i64, i64, ci, ci, vp, i64, vp, ci]
+        L.etn_fill_synthetic.argtypes = [ctypes.c_uint64, i64, i64, i64, i64, i64, ci, vp, vp]
+        _lib = L
+    return _lib
+
+
+def strerror(code: int) -> str:
+    return lib().etn_strerror(code).decode()
+
+
+def check(code: int, where: str) -> None:
+    if code != 0:
+        raise EtnError(code, strerror(code), where)
+
+
+def dtype_code(dt) -> int:
+    dt = np.dtype(dt)
+    if dt == np.float32:
+        return F32
+    if dt == np.float64:
+        return F64
+    raise TypeError(f"unsupported element type {dt} (float32 or float64)")
+
+
+# --------------------------------------------------------------------------- init ----
+def init(device_ids: list[int] | None = None) -> int:
+    """etn_init; returns the number of bound devices."""
+    if device_ids:
+        arr = (ctypes.c_int * len(device_ids))(*device_ids)
+        check(lib().etn_init(arr, len(device_ids)), "etn_init")
+    else:
+        check(lib().etn_init(None, 0), "etn_init")
+    return lib().etn_device_count()
+
+
+def shutdown() -> None:
+    lib().etn_shutdown()
+
+
+# ------------------------------------------------------------------ pinned buffers ----
+class PinnedBuffer:
+    """Page-locked host memory from etn_alloc_pinned, viewed as a numpy array."""
+
+    def __init__(self, nbytes: int):
+        self.nbytes = int(nbytes)
+        self.ptr = lib().etn_alloc_pinned(self.nbytes) if self.nbytes else None
+        if self.nbytes and not self.ptr:
+            raise MemoryError(f"etn_alloc_pinned({self.nbytes}) failed")
+
+    def array(self, shape, dtype) -> np.ndarray:
+        dtype = np.dtype(dtype)
+        n = int(np.prod(shape)) * dtype.itemsize
+        if n > self.nbytes:
+            raise ValueError("view larger than the buffer")
+        if n == 0:
+            return np.empty(shape, dtype=dtype)
+        buf = (ctypes.c_char * n).from_address(self.ptr)
+        return np.frombuffer(buf, dtype=dtype).reshape(shape)
+
+    def free(self) -> None:
+        if self.ptr:
+            lib().etn_free_pinned(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+# ------------------------------------------------------------------- host entry ----
+def truncate_norm_host(x: np.ndarray, k: int, mode: int = TRUNCATE_RENORM, out: np.ndarray | None = None,
+                       n_devices: int = 0) -> np.ndarray:
+    """embed_truncate_norm_host on a C-contiguous-row [batch x D] host array (pinned or not)."""
+    if x.ndim != 2 or x.strides[1] != x.itemsize:
+        raise ValueError("x must be 2-D with unit column stride")
+    batch, D = x.shape
+    kk = min(int(k), D) if k > 0 else 0
+    if out is None:
+        out = np.empty((batch, max(kk, 0)), dtype=x.dtype)
+    pitch = x.strides[0] if batch > 1 else D * x.itemsize
+    check(lib().embed_truncate_norm_host(batch, D, k, dtype_code(x.dtype), mode,
+                                         x.ctypes.data if batch else None, pitch,
+                                         out.ctypes.data if batch else None, n_devices),
+          "embed_truncate_norm_host")
+    return out
+
+
+# --------------------------------------------------------- reference call-site mirror ----
+def getenv_int(key: str, default: int, env=None) -> int:
+    """config.GetenvInt (config.go:17-24): unset, empty or not an integer -> default."""
+    env = os.environ if env is None else env
+    v = env.get(key, "")
+    if v == "":
+        return default
+    body = v[1:] if v[:1] in "+-" else v
+    if not body or not body.isascii() or not body.isdigit():
+        return default
+    n = int(v)
+    return n if -(1 << 63) <= n < (1 << 63) else default
+
+
+def resolve_dims(req_dimensions: int, env=None) -> int:
+    """handlers.go:1874-1877: the request's `dimensions`, else CLOUD_EMBED_DIMENSIONS."""
+    return req_dimensions if req_dimensions != 0 else getenv_int("CLOUD_EMBED_DIMENSIONS", 0, env)
+
+
+def renorm_enabled(env=None) -> bool:
+    """EMBED_RENORMALIZE=1 switches the handler from the reference's truncate-only
+    behaviour to truncate+renormalise.  Default off: renormalising changes response values
+    relative to the reference."""
+    return getenv_int("EMBED_RENORMALIZE", 0, env) == 1
+
+
+def _packable(emb: list) -> bool:
+    return all(type(v) in (float, int) for v in emb)
+
+
+def truncate_embeddings(result: Any, dims: int, renorm: bool | None = None) -> dict:
+    """GPU drop-in for ``truncateEmbeddings(result, dims)`` (handlers.go:2062-2078).
+
+    Same contract as the reference, item by item: ``data`` that is not a list is a no-op;
+    non-dict items are skipped; an ``embedding`` that is not a list (base64 string, null) is
+    left alone; vectors with ``len <= dims`` are left whole; longer ones keep their first
+    ``dims`` components in order.  With ``renorm`` (default: EMBED_RENORMALIZE) the kept
+    prefix is L2-renormalised as well.  Vectors are packed per source length into pinned
+    buffers and each group goes through one ``embed_truncate_norm_host`` call; a vector
+    holding anything but JSON numbers cannot be packed and gets the reference reslice.
+    Returns counters {"gpu_vectors", "resliced_vectors", "launch_groups"}.
+    """
+    stats = {"gpu_vectors": 0, "resliced_vectors": 0, "launch_groups": 0}
+    if renorm is None:
+        renorm = renorm_enabled()
+    if not isinstance(result, dict) or dims <= 0:
+        return stats
+    data = result.get("data")
+    if not isinstance(data, list):
+        return stats
+    groups: dict[int, list[dict]] = {}
+    for item in data:
+        if not isinstance(item, dict):
+            continue
+        emb = item.get("embedding")
+        if not isinstance(emb, list) or len(emb) <= dims:
+            continue
+        if _packable(emb):
+            groups.setdefault(len(emb), []).append(item)
+        else:
+            item["embedding"] = emb[:dims]
+            stats["resliced_vectors"] += 1
+    mode = TRUNCATE_RENORM if renorm else TRUNCATE
+    for D, items in groups.items():
+        n = len(items)
+        pin_in, pin_out = PinnedBuffer(n * D * 8), PinnedBuffer(n * dims * 8)
+        try:
+            x = pin_in.array((n, D), np.float64)
+            for r, item in enumerate(items):
+                x[r] = item["embedding"]
+            y = truncate_norm_host(x, dims, mode, out=pin_out.array((n, dims), np.float64))
+            for r, item in enumerate(items):
+                item["embedding"] = y[r].tolist()
+        finally:
+            pin_in.free()
+            pin_out.free()
+        stats["gpu_vectors"] += n
+        stats["launch_groups"] += 1
+    return stats

@@ -1,0 +1,118 @@
+"""-m gpu tests of the host-buffer path (embed_truncate_norm_host) and of the host-side
+mirror of the reference call site, truncate_embeddings(result, dims)
+(reference: core/internal/api/handlers.go:1891-1893, 2062-2078)."""
+import copy
+import json
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+if not torch.cuda.is_available():
+    pytest.skip("no CUDA device", allow_module_level=True)
+
+from llm_mcp_b200 import embedgpu as eg  # noqa: E402
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _init():
+    assert eg.init() >= 1
+    yield
+    eg.shutdown()
+
+
+def _ulp(oracle, got, want, bar=2):
+    d, i = oracle.max_ulp(got, want)
+    assert 0 <= d <= bar, (d, i)
+
+
+@pytest.mark.parametrize("rows,D,k,dt", [
+    (1024, 4096, 1024, np.float64),        # C1 through the handler-facing call
+    (70000, 768, 256, np.float32),         # several chunks, ragged last chunk
+    (5000, 770, 257, np.float32), (3, 40, 39, np.float64), (17, 48, 100, np.float32),
+])
+def test_host_path_against_oracle(oracle, rows, D, k, dt):
+    xh = oracle.fill(3, rows, D, dt)
+    for pinned in (False, True):
+        if pinned:
+            pin = eg.PinnedBuffer(xh.nbytes)
+            x = pin.array(xh.shape, dt)
+            x[:] = xh
+        else:
+            x = xh
+        got = eg.truncate_norm_host(x, k, eg.TRUNCATE_RENORM)
+        _ulp(oracle, got, oracle.renorm_exact(xh, k))
+        got = eg.truncate_norm_host(x, k, eg.TRUNCATE)
+        assert np.array_equal(got, oracle.truncate(xh, k))
+        if pinned:
+            del x
+            pin.free()
+
+
+def test_host_path_row_pitch(oracle):
+    wide = oracle.fill(4, 4000, 1100, np.float32)
+    x = wide[:, :1024]                        # pitch 1100*4 > D*4
+    got = eg.truncate_norm_host(x, 256)
+    _ulp(oracle, got, oracle.renorm_exact(np.ascontiguousarray(x), 256))
+
+
+def test_host_path_large_multi_chunk(oracle):
+    rows, D, k = 262144, 1024, 256            # 256 MiB prefix -> 8 staging chunks
+    pin_in, pin_out = eg.PinnedBuffer(rows * D * 4), eg.PinnedBuffer(rows * k * 4)
+    x = pin_in.array((rows, D), np.float32)
+    x[:] = oracle.fill(6, rows, D, np.float32)
+    y = eg.truncate_norm_host(x, k, out=pin_out.array((rows, k), np.float32))
+    idx = np.r_[0:64, rows // 2:rows // 2 + 64, rows - 64:rows]
+    _ulp(oracle, y[idx], oracle.renorm_exact(x[idx], k))
+    n = np.sqrt((y.astype(np.float64) ** 2).sum(1))
+    assert np.abs(n - 1).max() < 2e-7
+    del x, y
+    pin_in.free(); pin_out.free()
+
+
+# ------------------------------------------------ reference call-site mirror ----
+def _response(oracle, n=37, D=1024, seed=8):
+    v = oracle.fill(seed, n, D, np.float64)
+    return {"object": "list", "model": "qwen/qwen3-embedding-8b",
+            "data": [{"object": "embedding", "index": i, "embedding": v[i].tolist()} for i in range(n)],
+            "usage": {"prompt_tokens": 11, "total_tokens": 11}}
+
+
+def test_mirror_truncate_equals_reference(oracle):
+    """Default mode: byte-for-byte what truncateEmbeddings produces, incl. the JSON text."""
+    r = _response(oracle)
+    r["data"][3]["embedding"] = r["data"][3]["embedding"][:100]       # shorter than dims: left whole
+    r["data"][5]["embedding"] = r["data"][5]["embedding"][:300]       # ragged lengths in one response
+    r["data"][7]["embedding"] = "AAAAAA=="                            # base64: untouched
+    r["data"][9]["embedding"] = None
+    r["data"].append("not-a-map")
+    r["data"].append({"index": 99})
+    r["data"][11]["embedding"] = r["data"][11]["embedding"][:299] + ["x", 1.0, 2.0]   # unpackable: resliced
+    want = copy.deepcopy(r)
+    oracle.truncate_embeddings_ref(want, 256)
+    stats = eg.truncate_embeddings(r, 256, renorm=False)
+    assert r == want
+    assert json.dumps(r, sort_keys=True) == json.dumps(want, sort_keys=True)
+    assert stats["gpu_vectors"] == 37 - 4 and stats["resliced_vectors"] == 1 and stats["launch_groups"] == 2
+
+
+def test_mirror_renorm(oracle):
+    r = _response(oracle, n=20, D=768)
+    ref = copy.deepcopy(r)
+    oracle.truncate_embeddings_ref(ref, 256)
+    eg.truncate_embeddings(r, 256, renorm=True)
+    for a, b in zip(r["data"], ref["data"]):
+        assert a["index"] == b["index"] and len(a["embedding"]) == 256
+        want = oracle.renorm_exact(np.array([b["embedding"]]), 256)[0]
+        _ulp(oracle, np.array(a["embedding"]), want)
+    assert r["usage"] == ref["usage"] and r["model"] == ref["model"]
+
+
+def test_mirror_dims_not_positive_is_noop(oracle):
+    r = _response(oracle, n=3, D=64)
+    keep = copy.deepcopy(r)
+    for dims in (0, -3):                      # handlers.go:1891: the op runs only when dims > 0
+        eg.truncate_embeddings(r, dims)
+        assert r == keep
