@@ -40,30 +40,43 @@ int sm_count(int dev, int* out) {
   return 0;
 }
 
-// Persistent grid: one full wave of resident blocks, or fewer if the batch is small.
+// Grid: one warp-iteration per row group (waves == 0, the hardware block scheduler balances
+// the SMs), or `waves` full waves of resident blocks looping grid-stride.
 template <typename K>
-int grid_for(K kernel, int64_t blocks_needed, int* grid) {
-  int dev = 0, sms = 0, per_sm = 0;
-  cudaError_t e = cudaGetDevice(&dev);
-  if (e != cudaSuccess) return (int)e;
-  if (int rc = sm_count(dev, &sms)) return rc;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, 0);
-  if (e != cudaSuccess) return (int)e;
-  if (per_sm < 1) per_sm = 1;
-  const int64_t cap = (int64_t)sms * per_sm;
+int grid_for(K kernel, int64_t blocks_needed, int waves, int* grid) {
+  int64_t cap = (int64_t)1 << 30;
+  if (waves > 0) {
+    int dev = 0, sms = 0, per_sm = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (int rc = sm_count(dev, &sms)) return rc;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, 0);
+    if (e != cudaSuccess) return (int)e;
+    cap = (int64_t)sms * std::max(per_sm, 1) * waves;
+  }
   *grid = (int)std::max<int64_t>(1, std::min<int64_t>(blocks_needed, cap));
   return 0;
 }
 
 // ------------------------------------------------------------- launchers ----
-// MINB = resident blocks per SM the register allocation is held to (bytes in flight per SM
-// = MINB * 8 warps * R*NV * 512 B).
-template <typename T, int NV, int R, int MODE, int MINB>
-int launch_reg(const void* in, void* out, int64_t batch, int64_t in_pitch, int nvec, cudaStream_t s) {
-  auto kern = rows_reg_kernel<T, NV, R, MODE, MINB>;
+// MINB = resident blocks per SM the register allocation is held to.
+template <typename T, int VB, int NV, int R, int L, int MODE, int MINB, bool RAGGED>
+int launch_reg(const void* in, void* out, int64_t batch, int64_t in_pitch, int nvec, int64_t D,
+               const int32_t* k_per_row, const int64_t* out_offsets, int waves, cudaStream_t s) {
+  auto kern = rows_reg_kernel<T, VB, NV, R, L, MODE, MINB, VB == 32 ? 1 : 0, RAGGED>;
   int grid = 0;
-  const int64_t rows_per_block = (int64_t)kWarpsPerBlock * R;
-  if (int rc = grid_for(kern, (batch + rows_per_block - 1) / rows_per_block, &grid)) return rc;
+  const int64_t rows_per_block = (int64_t)kWarpsPerBlock * R * (32 / L);
+  if (int rc = grid_for(kern, (batch + rows_per_block - 1) / rows_per_block, waves, &grid)) return rc;
+  kern<<<grid, kThreads, 0, s>>>((const char*)in, (char*)out, batch, in_pitch, nvec, D, k_per_row, out_offsets);
+  return (int)cudaGetLastError();
+}
+
+template <typename T, int VB, int NV, int G, int MODE, int MINB>
+int launch_coop(const void* in, void* out, int64_t batch, int64_t in_pitch, int nvec, cudaStream_t s) {
+  auto kern = rows_coop_kernel<T, VB, NV, G, MODE, MINB, VB == 32 ? 1 : 0>;
+  int grid = 0;
+  const int64_t rows_per_block = kWarpsPerBlock / G;
+  if (int rc = grid_for(kern, (batch + rows_per_block - 1) / rows_per_block, 0, &grid)) return rc;
   kern<<<grid, kThreads, 0, s>>>((const char*)in, (char*)out, batch, in_pitch, nvec);
   return (int)cudaGetLastError();
 }
@@ -73,33 +86,71 @@ int launch_general(const void* in, void* out, int64_t batch, int64_t D, int64_t 
                    const int32_t* k_per_row, const int64_t* out_offsets, cudaStream_t s) {
   auto kern = rows_general_kernel<T, MODE>;
   int grid = 0;
-  if (int rc = grid_for(kern, (batch + kWarpsPerBlock - 1) / kWarpsPerBlock, &grid)) return rc;
+  if (int rc = grid_for(kern, (batch + kWarpsPerBlock - 1) / kWarpsPerBlock, 0, &grid)) return rc;
   kern<<<grid, kThreads, 0, s>>>((const T*)in, (T*)out, batch, D, k, k_per_row, out_offsets);
   return (int)cudaGetLastError();
 }
 
-// Dense rows: the register-row kernel when both sides are 16-byte tileable and the prefix
-// fits 16 vectors per lane (8 KiB per row); the general kernel otherwise.
+// Dense rows.  Kernel choice by prefix size and alignment:
+//   32-byte tileable: rows_reg (<= 8 KiB per row), rows_coop with 2/4/8 warps per row (<= 64 KiB)
+//   16-byte tileable: rows_reg with 128-bit accesses (<= 8 KiB)
+//   anything else:    rows_general
+// Truncation moves bytes, so one instantiation (T = float) serves both element types.
 template <typename T, int MODE>
 int launch_dense(const void* in, void* out, int64_t batch, int64_t D, int64_t kk, cudaStream_t s) {
+  using TT = typename std::conditional<MODE == kModeTruncate, float, T>::type;
+  // float64 renorm carries the compensated sum and the double-double scale: more registers
+  // per thread, so fewer rows per warp and fewer resident blocks (tools/tune.cu, profiles/).
+  constexpr bool heavy = MODE == kModeRenorm && sizeof(T) == 8;
+  constexpr int R1 = heavy ? 2 : 4, R2 = heavy ? 1 : 2;
+  constexpr int MB = 4, MB4 = heavy ? 3 : 4, MB8 = heavy ? 2 : 4;
   const int64_t in_pitch = D * (int64_t)sizeof(T);
   const int64_t k_bytes = kk * (int64_t)sizeof(T);
-  const bool tileable = aligned_to(in, 16) && aligned_to(out, 16) && in_pitch % 16 == 0 &&
-                        k_bytes % 16 == 0;
-  if (tileable && k_bytes <= 16 * 512) {
+  const int W = 0;                                                  // one row group per warp
+  if (aligned_to(in, 32) && aligned_to(out, 32) && in_pitch % 32 == 0 && k_bytes % 32 == 0 &&
+      k_bytes <= 64 * 1024) {
+    const int nvec = (int)(k_bytes / 32);
+    const int nv = (nvec + 31) / 32;
+    // short rows: 8 or 16 lanes per row, so a warp finishes 4 or 2 rows per reduction
+    constexpr int RS = heavy ? 2 : 8, MBS = heavy ? 4 : 2;
+    if (nvec <= 8)  return launch_reg<TT, 32, 1, RS, 8, MODE, MBS, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
+    if (nvec <= 16) return launch_reg<TT, 32, 1, RS, 16, MODE, MBS, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
+    if (nv <= 1) return launch_reg<TT, 32, 1, R1, 32, MODE, MB, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
+    if (nv <= 2) return launch_reg<TT, 32, 2, R2, 32, MODE, MB, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
+    if (nv <= 4) return launch_reg<TT, 32, 4, 1, 32, MODE, MB4, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
+    if (nv <= 8) {
+      if constexpr (heavy) return launch_reg<TT, 32, 8, 1, 32, MODE, MB8, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
+      else return launch_coop<TT, 32, 4, 2, MODE, 4>(in, out, batch, in_pitch, nvec, s);
+    }
+    if (nv <= 16) return launch_coop<TT, 32, 4, 4, MODE, MB4>(in, out, batch, in_pitch, nvec, s);
+    if (nv <= 32) return launch_coop<TT, 32, 4, 8, MODE, MB4>(in, out, batch, in_pitch, nvec, s);
+    return launch_coop<TT, 32, 8, 8, MODE, MB8>(in, out, batch, in_pitch, nvec, s);
+  }
+  if (aligned_to(in, 16) && aligned_to(out, 16) && in_pitch % 16 == 0 && k_bytes % 16 == 0 &&
+      k_bytes <= 16 * 512) {
     const int nvec = (int)(k_bytes / 16);
     const int nv = (nvec + 31) / 32;
-    // Truncation moves bytes; one instantiation (T = float) serves both element types.
-    using TT = typename std::conditional<MODE == kModeTruncate, float, T>::type;
-    constexpr int MB = MODE == kModeTruncate ? 4 : (sizeof(T) == 4 ? 4 : 2);
-    constexpr int MB16 = (MODE == kModeRenorm && sizeof(T) == 8) ? 1 : 2;
-    if (nv <= 1)  return launch_reg<TT, 1, 8, MODE, MB>(in, out, batch, in_pitch, nvec, s);
-    if (nv <= 2)  return launch_reg<TT, 2, 4, MODE, MB>(in, out, batch, in_pitch, nvec, s);
-    if (nv <= 4)  return launch_reg<TT, 4, 2, MODE, MB>(in, out, batch, in_pitch, nvec, s);
-    if (nv <= 8)  return launch_reg<TT, 8, 1, MODE, MB>(in, out, batch, in_pitch, nvec, s);
-    return launch_reg<TT, 16, 1, MODE, MB16>(in, out, batch, in_pitch, nvec, s);
+    if (nvec <= 8)  return launch_reg<TT, 16, 1, 2 * R1, 8, MODE, MB, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
+    if (nvec <= 16) return launch_reg<TT, 16, 1, 2 * R1, 16, MODE, MB, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
+    if (nv <= 1) return launch_reg<TT, 16, 1, 2 * R1, 32, MODE, MB, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
+    if (nv <= 2) return launch_reg<TT, 16, 2, R1, 32, MODE, MB, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
+    if (nv <= 4) return launch_reg<TT, 16, 4, R2, 32, MODE, MB, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
+    if (nv <= 8) return launch_reg<TT, 16, 8, 1, 32, MODE, MB4, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
+    return launch_reg<TT, 16, 16, 1, 32, MODE, MB8, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
   }
   return launch_general<T, MODE>(in, out, batch, D, kk, nullptr, nullptr, s);
+}
+
+// Ragged rows: a warp per row with room for 8 KiB of prefix in registers when the input is
+// 32-byte tileable (rows that are not, or are longer, fall back inside the kernel).
+template <typename T, int MODE>
+int launch_ragged(const void* in, void* out, int64_t batch, int64_t D, const int32_t* k_per_row,
+                  const int64_t* out_offsets, cudaStream_t s) {
+  constexpr bool heavy = MODE == kModeRenorm && sizeof(T) == 8;
+  const int64_t in_pitch = D * (int64_t)sizeof(T);
+  if (aligned_to(in, 32) && aligned_to(out, 32) && in_pitch % 32 == 0)
+    return launch_reg<T, 32, 8, 1, 32, MODE, heavy ? 2 : 3, true>(in, out, batch, in_pitch, 0, D, k_per_row, out_offsets, 0, s);
+  return launch_general<T, MODE>(in, out, batch, D, 0, k_per_row, out_offsets, s);
 }
 
 int check_dense(int64_t batch, int64_t D, int64_t k, int dtype, const void* in, const void* out) {
@@ -242,12 +293,10 @@ int embed_truncate_norm_ragged(int64_t batch, int64_t D, const int32_t* k_per_ro
     return ETN_ERR_ALIGN;
   cudaStream_t s = (cudaStream_t)stream;
   if (mode == ETN_TRUNCATE)
-    return dtype == ETN_F32
-               ? launch_general<float, kModeTruncate>(in, out, batch, D, 0, k_per_row, out_offsets, s)
-               : launch_general<double, kModeTruncate>(in, out, batch, D, 0, k_per_row, out_offsets, s);
-  return dtype == ETN_F32
-             ? launch_general<float, kModeRenorm>(in, out, batch, D, 0, k_per_row, out_offsets, s)
-             : launch_general<double, kModeRenorm>(in, out, batch, D, 0, k_per_row, out_offsets, s);
+    return dtype == ETN_F32 ? launch_ragged<float, kModeTruncate>(in, out, batch, D, k_per_row, out_offsets, s)
+                            : launch_ragged<double, kModeTruncate>(in, out, batch, D, k_per_row, out_offsets, s);
+  return dtype == ETN_F32 ? launch_ragged<float, kModeRenorm>(in, out, batch, D, k_per_row, out_offsets, s)
+                          : launch_ragged<double, kModeRenorm>(in, out, batch, D, k_per_row, out_offsets, s);
 }
 
 int etn_init(const int* device_ids, int n_devices) {

@@ -4,16 +4,23 @@
 // (/root/reference/core/internal/api/handlers.go:2068-2076) on a packed row-major matrix:
 // keep the first k of D components of every row and, in RENORM mode, divide them by their
 // L2 norm.  It is a bandwidth-bound streaming reduction (3 flops per 2*sizeof(T) bytes), so
-// there are no tensor cores here: the kernels are built around 16-byte coalesced loads of
-// the row prefix only, whole rows held in registers between the load and the store, and a
-// warp-shuffle reduction.
+// there are no tensor cores here.  Every kernel reads only the k-prefix of a row, keeps the
+// whole prefix in registers between its one load and its one store, and reduces with warp
+// shuffles:
 //
-// Numerics (bar: <= 4 ulp of the exactly rounded quotient, see tests/):
+//   rows_reg_kernel   one warp owns R whole rows (prefix <= 8 KiB), 256-bit LDG/STG
+//   rows_coop_kernel  G warps of a block share one row (prefix <= 64 KiB), partial sums
+//                     meet in shared memory behind a named barrier
+//   rows_general_kernel  any k / D / element alignment, two passes, second from L1/L2
+//
+// Numerics (bar: <= 4 ulp of the exactly rounded quotient; documented: <= 2 ulp):
 //   float32  squares are exact in float64 and are summed there; the scale 1/sqrt(ss) is
-//            rounded to float32 once and applied with one multiply  -> <= 1.5 ulp.
-//   float64  the sum of squares is carried as an error-free (sum, compensation) pair
-//            (TwoProduct by FMA + TwoSum), the reciprocal norm as a double-double
-//            (r, r_lo) from one Newton correction, and y = fma(x, r, x*r_lo) -> ~0.5 ulp.
+//            rounded to float32 once and applied with one multiply        -> <= 1.5 ulp.
+//   float64  squares are summed in blocks of <= 4 by FMA, and the block sums are added with
+//            an error-free TwoSum into a (sum, compensation) pair, so the sum of squares
+//            carries a relative error <= 4 * 2^-53 however long the row is; the reciprocal
+//            norm is a double-double (r, r_lo) from one Newton correction and
+//            y = fma(x, r, x*r_lo)                                         -> <= 1.5 ulp.
 //   Rows whose squares would overflow/underflow are rescaled by a power of two first;
 //   all-zero rows are copied.  Both are warp-uniform slow paths.
 #pragma once
@@ -29,65 +36,54 @@ constexpr int kWarpsPerBlock = 8;
 constexpr int kThreads = kWarpsPerBlock * 32;
 constexpr unsigned kFull = 0xffffffffu;
 
-// ------------------------------------------------------------ memory access ----
-// Input is read exactly once and output written exactly once: keep both out of L1.
-__device__ __forceinline__ uint4 ld_stream16(const void* p) {
-  uint4 v;
-  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
-               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
-  return v;
-}
-__device__ __forceinline__ void st_stream16(void* p, const uint4& v) {
-  asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};"
-               :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
-}
-
 // -------------------------------------------------------------- reductions ----
+// Butterflies over groups of L consecutive lanes (L = 32: the whole warp).  Every lane of a
+// group ends up with the same value.  All 32 lanes must take part.
+template <int L = 32>
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
+  for (int o = L / 2; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
   return v;
 }
+template <int L = 32>
 __device__ __forceinline__ double warp_max(double v) {
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(kFull, v, o));
+  for (int o = L / 2; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(kFull, v, o));
   return v;
 }
 
-// Error-free accumulator of squares: value = s + c exactly up to O(eps^2).
+// Compensated accumulator of non-negative terms: value = s + c, error O(eps^2) per add.
 struct Acc2 {
   double s, c;
   __device__ __forceinline__ void clear() { s = 0.0; c = 0.0; }
-  __device__ __forceinline__ void add_square(double x) {
-    double p = x * x;
-    double e = fma(x, x, -p);            // TwoProduct: x*x = p + e exactly
-    double t = s + p;                    // TwoSum (Knuth): s + p = t + err exactly
-    double bp = t - s;
-    double err = (s - (t - bp)) + (p - bp);
+  __device__ __forceinline__ void add(double q) {           // TwoSum (Knuth): s + q = t + err
+    const double t = s + q;
+    const double bp = t - s;
+    const double err = (s - (t - bp)) + (q - bp);
     s = t;
-    c += err + e;
+    c += err;
   }
-  __device__ __forceinline__ void merge(double os, double oc) {
-    double t = s + os;
-    double bp = t - s;
-    double err = (s - (t - bp)) + (os - bp);
-    s = t;
-    c += oc + err;
-  }
+  __device__ __forceinline__ void merge(double os, double oc) { add(os); c += oc; }
+  template <int L = 32>
   __device__ __forceinline__ void warp_reduce() {
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      double os = __shfl_xor_sync(kFull, s, o);
-      double oc = __shfl_xor_sync(kFull, c, o);
+    for (int o = L / 2; o > 0; o >>= 1) {
+      const double os = __shfl_xor_sync(kFull, s, o);
+      const double oc = __shfl_xor_sync(kFull, c, o);
       merge(os, oc);
     }
+  }
+  // hi + lo = s + c with hi = fl(s + c)
+  __device__ __forceinline__ void split(double& hi, double& lo) const {
+    hi = s + c;
+    lo = (s - hi) + c;
   }
 };
 
 // ------------------------------------------------------------ row scaling ----
 enum : int { kCopy = 0, kFast = 1, kSlow = 2 };
 
-// float32 rows.  ss = exact-ish float64 sum of squares (never overflows for float input).
+// float32 rows.  ss = float64 sum of squares (cannot overflow for float input).
 struct Scale32 {
   int kind;
   float inv_f;
@@ -109,13 +105,13 @@ struct Scale32 {
 // exponent applied to x first (slow path only).
 struct Scale64 {
   int kind;
-  int pre;           // x is multiplied by 2^pre before use when kind == kSlow
+  int pre;
   double r, r_lo;
   // ss_hi + ss_lo = sum of squares (of the possibly pre-scaled row), ss_hi normal and finite.
   __device__ __forceinline__ void from_ss(double ss_hi, double ss_lo) {
     r = rsqrt(ss_hi);                              // <= 1 ulp
-    double t = ss_hi * r;
-    double te = fma(ss_hi, r, -t);                 // ss_hi*r = t + te
+    const double t = ss_hi * r;
+    const double te = fma(ss_hi, r, -t);           // ss_hi*r = t + te
     double h = fma(t, r, -1.0);                    // ss*r^2 - 1, leading part
     h += fma(te, r, ss_lo * r * r);
     r_lo = -0.5 * h * r;                           // Newton: 1/sqrt(ss) = r*(1 - h/2)
@@ -132,35 +128,258 @@ __device__ __forceinline__ bool ss_in_range(double ss) {
   return ss >= 0x1p-900 && ss <= DBL_MAX;
 }
 
-// ------------------------------------------------------- register-row kernel ----
-// One warp owns R rows at a time; each lane holds NV 16-byte vectors of every row, i.e. the
-// whole k-prefix of R rows sits in registers between the load and the store.  All R*NV
-// loads of an iteration are issued before anything is consumed (memory-level parallelism).
-// Requires 16-byte aligned rows on both sides; nvec = 16-byte vectors per row prefix.
-template <typename T> struct VecTraits;
-template <> struct VecTraits<float>  { static constexpr int kPer = 4; };
-template <> struct VecTraits<double> { static constexpr int kPer = 2; };
+// ---------------------------------------------------------- vector access ----
+// Input is read exactly once and output written exactly once: no L1 allocation; with the
+// 256-bit forms (sm_100) also L2::evict_first when HINT == 1.
+template <int VB, int HINT>
+__device__ __forceinline__ void ld_vec(uint32_t* w, const void* p) {
+  if constexpr (VB == 16) {
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "l"(p));
+  } else if constexpr (HINT == 1) {
+    asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
+                 : "l"(p));
+  } else {
+    asm volatile("ld.global.nc.L1::no_allocate.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
+                 : "l"(p));
+  }
+}
+template <int VB, int HINT>
+__device__ __forceinline__ void st_vec(void* p, const uint32_t* w) {
+  if constexpr (VB == 16) {
+    asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]) : "memory");
+  } else if constexpr (HINT == 1) {
+    asm volatile("st.global.L1::no_allocate.L2::evict_first.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                 :: "l"(p), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7])
+                 : "memory");
+  } else {
+    asm volatile("st.global.L1::no_allocate.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                 :: "l"(p), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7])
+                 : "memory");
+  }
+}
 
-template <typename T, int NV, int R, int MODE, int MINB>
+__device__ __forceinline__ double words_to_double(const uint32_t* w) {
+  return __hiloint2double((int)w[1], (int)w[0]);
+}
+__device__ __forceinline__ void double_to_words(uint32_t* w, double v) {
+  w[0] = (unsigned)__double2loint(v); w[1] = (unsigned)__double2hiint(v);
+}
+
+// ------------------------------------------- per-lane pieces of a row in registers ----
+// Sum of squares of the NW words a lane holds, float32 elements: plain float64 FMA chains.
+template <int NW>
+__device__ __forceinline__ double lane_sumsq32(const uint32_t (&w)[NW]) {
+  double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+  for (int i = 0; i < NW; i += 2) {
+    const double x0 = (double)__uint_as_float(w[i]);
+    const double x1 = (double)__uint_as_float(w[i + 1]);
+    a0 = fma(x0, x0, a0); a1 = fma(x1, x1, a1);
+  }
+  return a0 + a1;
+}
+
+// float64 elements: blocks of <= 4 squares by FMA, block sums added error-free.
+// `pre` != 0 rescales by 2^pre first (slow path).
+template <int NW>
+__device__ __forceinline__ void lane_sumsq64(const uint32_t (&w)[NW], int pre, Acc2& acc) {
+  constexpr int ND = NW / 2;
+  acc.clear();
+#pragma unroll
+  for (int b = 0; b < ND; b += 4) {
+    double q = 0.0;
+#pragma unroll
+    for (int i = b; i < b + 4 && i < ND; ++i) {
+      double x = words_to_double(&w[2 * i]);
+      if (pre != 0) x = scalbn(x, pre);
+      q = fma(x, x, q);
+    }
+    acc.add(q);
+  }
+}
+
+template <int NW>
+__device__ __forceinline__ double lane_maxabs64(const uint32_t (&w)[NW]) {
+  double m = 0.0;
+#pragma unroll
+  for (int i = 0; i < NW / 2; ++i) m = fmax(m, fabs(words_to_double(&w[2 * i])));
+  return m;
+}
+
+template <int NW>
+__device__ __forceinline__ void lane_apply32(uint32_t (&w)[NW], const Scale32& sc) {
+  if (sc.kind == kFast) {                            // warp-uniform
+    const float f = sc.inv_f;
+#pragma unroll
+    for (int i = 0; i < NW; ++i) w[i] = __float_as_uint(__uint_as_float(w[i]) * f);
+  } else if (sc.kind == kSlow) {
+    const double d = sc.inv_d;
+#pragma unroll
+    for (int i = 0; i < NW; ++i) w[i] = __float_as_uint((float)((double)__uint_as_float(w[i]) * d));
+  }
+}
+
+template <int NW>
+__device__ __forceinline__ void lane_apply64(uint32_t (&w)[NW], const Scale64& sc) {
+  if (sc.kind == kCopy) return;
+#pragma unroll
+  for (int i = 0; i < NW / 2; ++i) double_to_words(&w[2 * i], sc.apply(words_to_double(&w[2 * i])));
+}
+
+// Scale of a float64 row held in registers by a group of L lanes.  Control flow is uniform
+// across the warp (the shuffles need all 32 lanes) even when the warp's 32/L rows disagree
+// on whether they need the rescaled slow path.
+template <int NW, int L>
+__device__ __forceinline__ Scale64 row_scale64(const uint32_t (&w)[NW]) {
+  Acc2 acc;
+  lane_sumsq64<NW>(w, 0, acc);
+  acc.warp_reduce<L>();
+  Scale64 sc; sc.pre = 0; sc.kind = kFast; sc.r = 0.0; sc.r_lo = 0.0;
+  double hi, lo;
+  acc.split(hi, lo);
+  const bool ok = ss_in_range(hi);
+  if (__all_sync(kFull, ok)) { sc.from_ss(hi, lo); return sc; }
+  // some row here is all zeros or has squares out of range: rescale by its largest magnitude
+  const double m = warp_max<L>(lane_maxabs64<NW>(w));
+  const bool copy = !ok && (!(m > 0.0) || !(m <= DBL_MAX));   // all zeros (or non-finite in)
+  const int pre = (ok || copy) ? 0 : -ilogb(m);
+  Acc2 a2;
+  lane_sumsq64<NW>(w, pre, a2);
+  a2.warp_reduce<L>();
+  if (ok) {
+    sc.from_ss(hi, lo);
+  } else if (copy) {
+    sc.kind = kCopy;
+  } else {
+    sc.kind = kSlow;
+    sc.pre = pre;
+    a2.split(hi, lo);
+    sc.from_ss(hi, lo);
+  }
+  return sc;
+}
+
+// ------------------------------------------------------ one row, one warp, any shape ----
+// Two passes over the row prefix with element-wise coalesced accesses; the second pass hits
+// L1/L2.  Used by rows_general_kernel and as the per-row fallback of the ragged path.
+template <typename T, int MODE>
+__device__ __forceinline__ void general_row(const T* __restrict__ x, T* __restrict__ y, int64_t kr,
+                                            int lane) {
+  if constexpr (MODE == kModeTruncate) {
+    for (int64_t i = lane; i < kr; i += 32) y[i] = x[i];
+  } else if constexpr (sizeof(T) == 4) {
+    double a = 0.0;
+    for (int64_t i = lane; i < kr; i += 32) { const double xv = (double)x[i]; a = fma(xv, xv, a); }
+    Scale32 sc; sc.from_ss(warp_sum(a));
+    if (sc.kind == kCopy) { for (int64_t i = lane; i < kr; i += 32) y[i] = x[i]; }
+    else { for (int64_t i = lane; i < kr; i += 32) y[i] = sc.apply(x[i]); }
+  } else {
+    auto sumsq = [&](int pre, Acc2& acc) {
+      acc.clear();
+      for (int64_t i = lane; i < kr; i += 128) {       // blocks of <= 4 elements per lane
+        double q = 0.0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          if (i + 32 * j < kr) {
+            double xv = x[i + 32 * j];
+            if (pre != 0) xv = scalbn(xv, pre);
+            q = fma(xv, xv, q);
+          }
+        }
+        acc.add(q);
+      }
+      acc.warp_reduce();
+    };
+    Acc2 acc;
+    sumsq(0, acc);
+    Scale64 sc; sc.pre = 0; sc.kind = kFast;
+    double hi, lo;
+    acc.split(hi, lo);
+    if (ss_in_range(hi)) {
+      sc.from_ss(hi, lo);
+    } else {
+      double m = 0.0;
+      for (int64_t i = lane; i < kr; i += 32) m = fmax(m, fabs((double)x[i]));
+      m = warp_max(m);
+      if (!(m > 0.0) || !(m <= DBL_MAX)) {
+        sc.kind = kCopy;
+      } else {
+        sc.kind = kSlow;
+        sc.pre = -ilogb(m);
+        sumsq(sc.pre, acc);
+        acc.split(hi, lo);
+        sc.from_ss(hi, lo);
+      }
+    }
+    if (sc.kind == kCopy) { for (int64_t i = lane; i < kr; i += 32) y[i] = x[i]; }
+    else { for (int64_t i = lane; i < kr; i += 32) y[i] = (T)sc.apply((double)x[i]); }
+  }
+}
+
+// ------------------------------------------------------- register-row kernel ----
+// A group of L lanes (L = 32, 16 or 8) owns a row; a warp therefore works on R * 32/L rows
+// at a time, and each lane holds NV vectors of VB bytes of its rows, so the whole k-prefix
+// sits in registers between the load and the store.  All loads of an iteration are issued
+// before anything is consumed (R*NV*VB*32 bytes per warp in flight).  Requires VB-aligned
+// rows on both sides; nvec = VB-byte vectors per prefix (<= NV*L).  L < 32 keeps short rows
+// (<= 512 B) from paying a whole warp's reduction and scale computation each.
+//
+// RAGGED (L = 32, R = 1): row r keeps k_per_row[r] elements, written at element offset
+// out_offsets[r].  Rows whose prefix is not VB-tileable, or longer than the registers hold,
+// take general_row.
+template <typename T, int VB, int NV, int R, int L, int MODE, int MINB, int HINT, bool RAGGED>
 __global__ void __launch_bounds__(kThreads, MINB)
 rows_reg_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t batch,
-                int64_t in_pitch /*bytes*/, int nvec) {
+                int64_t in_pitch /*bytes*/, int nvec_dense, int64_t D,
+                const int32_t* __restrict__ k_per_row, const int64_t* __restrict__ out_offsets) {
+  static_assert(!RAGGED || (L == 32 && R == 1), "ragged rows are one per warp");
+  constexpr int W = VB / 4, NW = NV * W;
+  constexpr int S = 32 / L;                            // rows side by side in a warp
   const int lane = threadIdx.x & 31;
+  const int sub = lane / L, sl = lane % L;
   const int64_t warp = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * kThreads) >> 5;
-  const int64_t out_pitch = (int64_t)nvec * 16;
 
-  for (int64_t row0 = warp * R; row0 < batch; row0 += nwarps * R) {
-    uint4 v[R][NV];
+  for (int64_t row0 = warp * (R * S); row0 < batch; row0 += nwarps * (R * S)) {
+    uint32_t w[R][NW];
+    int nvec[R];
+    char* dst[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-      const bool row_ok = row0 + r < batch;
-      const char* src = in + (row0 + r) * in_pitch;
+      const int64_t row = row0 + r * S + sub;
+      const bool row_ok = row < batch;
+      const char* src = in + row * in_pitch;
+      nvec[r] = row_ok ? nvec_dense : 0;
+      dst[r] = out + row * ((int64_t)nvec_dense * VB);
+      if constexpr (RAGGED) {
+        if (row_ok) {
+          int64_t kr = k_per_row[row];
+          if (kr > D) kr = D;
+          const int64_t kb = kr * (int64_t)sizeof(T);
+          dst[r] = out + out_offsets[row] * (int64_t)sizeof(T);
+          const bool tile = (kb % VB == 0) && (kb <= (int64_t)NV * 32 * VB) &&
+                            ((reinterpret_cast<uintptr_t>(dst[r]) % VB) == 0);
+          if (tile) {
+            nvec[r] = (int)(kb / VB);
+          } else {                                     // warp-uniform: odd row, slow path
+            nvec[r] = 0;
+            general_row<T, MODE>((const T*)src, (T*)dst[r], kr, lane);
+          }
+        }
+      }
 #pragma unroll
       for (int j = 0; j < NV; ++j) {
-        const int idx = j * 32 + lane;
-        if (row_ok && idx < nvec) v[r][j] = ld_stream16(src + (int64_t)idx * 16);
-        else v[r][j] = make_uint4(0u, 0u, 0u, 0u);
+        const int idx = j * L + sl;
+        if (idx < nvec[r]) {
+          ld_vec<VB, HINT>(&w[r][j * W], src + (int64_t)idx * VB);
+        } else {
+#pragma unroll
+          for (int q = 0; q < W; ++q) w[r][j * W + q] = 0u;
+        }
       }
     }
 
@@ -168,119 +387,133 @@ rows_reg_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t bat
       if constexpr (sizeof(T) == 4) {
         double ss[R];
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-          double a0 = 0.0, a1 = 0.0;
+        for (int r = 0; r < R; ++r) ss[r] = lane_sumsq32<NW>(w[r]);
 #pragma unroll
-          for (int j = 0; j < NV; ++j) {
-            const double x0 = (double)__uint_as_float(v[r][j].x);
-            const double x1 = (double)__uint_as_float(v[r][j].y);
-            const double x2 = (double)__uint_as_float(v[r][j].z);
-            const double x3 = (double)__uint_as_float(v[r][j].w);
-            a0 = fma(x0, x0, a0); a1 = fma(x1, x1, a1);
-            a0 = fma(x2, x2, a0); a1 = fma(x3, x3, a1);
-          }
-          ss[r] = a0 + a1;
-        }
-        // R independent butterflies, interleaved
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
+        for (int o = L / 2; o > 0; o >>= 1) {          // R independent butterflies, interleaved
 #pragma unroll
           for (int r = 0; r < R; ++r) ss[r] += __shfl_xor_sync(kFull, ss[r], o);
         }
 #pragma unroll
         for (int r = 0; r < R; ++r) {
           Scale32 sc; sc.from_ss(ss[r]);
-          if (sc.kind == kFast) {                    // warp-uniform
-            const float f = sc.inv_f;
-#pragma unroll
-            for (int j = 0; j < NV; ++j) {
-              v[r][j].x = __float_as_uint(__uint_as_float(v[r][j].x) * f);
-              v[r][j].y = __float_as_uint(__uint_as_float(v[r][j].y) * f);
-              v[r][j].z = __float_as_uint(__uint_as_float(v[r][j].z) * f);
-              v[r][j].w = __float_as_uint(__uint_as_float(v[r][j].w) * f);
-            }
-          } else if (sc.kind == kSlow) {
-            const double d = sc.inv_d;
-#pragma unroll
-            for (int j = 0; j < NV; ++j) {
-              v[r][j].x = __float_as_uint((float)((double)__uint_as_float(v[r][j].x) * d));
-              v[r][j].y = __float_as_uint((float)((double)__uint_as_float(v[r][j].y) * d));
-              v[r][j].z = __float_as_uint((float)((double)__uint_as_float(v[r][j].z) * d));
-              v[r][j].w = __float_as_uint((float)((double)__uint_as_float(v[r][j].w) * d));
-            }
-          }
+          lane_apply32<NW>(w[r], sc);
         }
       } else {
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-          Acc2 acc; acc.clear();
-#pragma unroll
-          for (int j = 0; j < NV; ++j) {
-            acc.add_square(__hiloint2double((int)v[r][j].y, (int)v[r][j].x));
-            acc.add_square(__hiloint2double((int)v[r][j].w, (int)v[r][j].z));
-          }
-          acc.warp_reduce();
-          Scale64 sc;
-          sc.pre = 0;
-          const double ss_hi = acc.s + acc.c;
-          if (ss_in_range(ss_hi)) {
-            sc.kind = kFast;
-            sc.from_ss(ss_hi, (acc.s - ss_hi) + acc.c);
-          } else {
-            // zero row, or squares out of range: rescale by the row's largest magnitude
-            double m = 0.0;
-#pragma unroll
-            for (int j = 0; j < NV; ++j) {
-              m = fmax(m, fabs(__hiloint2double((int)v[r][j].y, (int)v[r][j].x)));
-              m = fmax(m, fabs(__hiloint2double((int)v[r][j].w, (int)v[r][j].z)));
-            }
-            m = warp_max(m);
-            if (!(m > 0.0) || !(m <= DBL_MAX)) {
-              sc.kind = kCopy;                       // all zeros (or non-finite in: pass through)
-            } else {
-              sc.kind = kSlow;
-              sc.pre = -ilogb(m);
-              Acc2 a2; a2.clear();
-#pragma unroll
-              for (int j = 0; j < NV; ++j) {
-                a2.add_square(scalbn(__hiloint2double((int)v[r][j].y, (int)v[r][j].x), sc.pre));
-                a2.add_square(scalbn(__hiloint2double((int)v[r][j].w, (int)v[r][j].z), sc.pre));
-              }
-              a2.warp_reduce();
-              const double h2 = a2.s + a2.c;
-              sc.from_ss(h2, (a2.s - h2) + a2.c);
-            }
-          }
-          if (sc.kind != kCopy) {
-#pragma unroll
-            for (int j = 0; j < NV; ++j) {
-              const double y0 = sc.apply(__hiloint2double((int)v[r][j].y, (int)v[r][j].x));
-              const double y1 = sc.apply(__hiloint2double((int)v[r][j].w, (int)v[r][j].z));
-              v[r][j].x = (unsigned)__double2loint(y0); v[r][j].y = (unsigned)__double2hiint(y0);
-              v[r][j].z = (unsigned)__double2loint(y1); v[r][j].w = (unsigned)__double2hiint(y1);
-            }
-          }
+          const Scale64 sc = row_scale64<NW, L>(w[r]);
+          lane_apply64<NW>(w[r], sc);
         }
       }
     }
 
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-      const bool row_ok = row0 + r < batch;
-      char* dst = out + (row0 + r) * out_pitch;
 #pragma unroll
       for (int j = 0; j < NV; ++j) {
-        const int idx = j * 32 + lane;
-        if (row_ok && idx < nvec) st_stream16(dst + (int64_t)idx * 16, v[r][j]);
+        const int idx = j * L + sl;
+        if (idx < nvec[r]) st_vec<VB, HINT>(dst[r] + (int64_t)idx * VB, &w[r][j * W]);
       }
     }
   }
 }
 
+// ---------------------------------------------------- cooperative-row kernel ----
+// G warps of a block share one row: vector slot j of warp g covers vectors
+// [(j*G + g)*32, (j*G + g + 1)*32) of the prefix, so a short prefix still spreads evenly.  Per-warp partial sums meet in shared memory behind a named barrier that
+// only the group's G*32 threads use, so groups (and their rare slow paths) never wait for
+// each other.  Prefix up to G*NV*32*VB bytes (64 KiB at G = 8, NV = 8, VB = 32).
+__device__ __forceinline__ void group_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(nthreads) : "memory");
+}
+
+template <typename T, int VB, int NV, int G, int MODE, int MINB, int HINT>
+__global__ void __launch_bounds__(kThreads, MINB)
+rows_coop_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t batch,
+                 int64_t in_pitch /*bytes*/, int nvec) {
+  constexpr int W = VB / 4, NW = NV * W;
+  constexpr int RPB = kWarpsPerBlock / G;            // rows per block iteration
+  __shared__ double part[2][kWarpsPerBlock][3];      // double-buffered: (s, c, max)
+  const int lane = threadIdx.x & 31;
+  const int wib = threadIdx.x >> 5;                  // warp in block
+  const int grp = wib / G, g = wib % G;
+  const int bar_id = 1 + grp;
+  const int64_t out_pitch = (int64_t)nvec * VB;
+  int ph = 0;
+
+  for (int64_t row = (int64_t)blockIdx.x * RPB + grp; row < batch; row += (int64_t)gridDim.x * RPB) {
+    uint32_t w[NW];
+    const char* src = in + row * in_pitch;
+    char* dst = out + row * out_pitch;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int idx = (j * G + g) * 32 + lane;
+      if (idx < nvec) {
+        ld_vec<VB, HINT>(&w[j * W], src + (int64_t)idx * VB);
+      } else {
+#pragma unroll
+        for (int q = 0; q < W; ++q) w[j * W + q] = 0u;
+      }
+    }
+
+    if constexpr (MODE == kModeRenorm) {
+      // exchange partials of the group; every warp then sums them in the same order
+      auto exchange = [&](double s, double c, double m, Acc2& tot, double& mx) {
+        if (lane == 0) { part[ph][wib][0] = s; part[ph][wib][1] = c; part[ph][wib][2] = m; }
+        group_sync(bar_id, G * 32);
+        tot.clear(); mx = 0.0;
+#pragma unroll
+        for (int i = 0; i < G; ++i) {
+          tot.merge(part[ph][grp * G + i][0], part[ph][grp * G + i][1]);
+          mx = fmax(mx, part[ph][grp * G + i][2]);
+        }
+        ph ^= 1;                                       // next exchange uses the other buffer
+      };
+      if constexpr (sizeof(T) == 4) {
+        const double a = warp_sum(lane_sumsq32<NW>(w));
+        Acc2 tot; double mx;
+        exchange(a, 0.0, 0.0, tot, mx);
+        Scale32 sc; sc.from_ss(tot.s + tot.c);
+        lane_apply32<NW>(w, sc);
+      } else {
+        Acc2 acc;
+        lane_sumsq64<NW>(w, 0, acc);
+        acc.warp_reduce();
+        const double m = warp_max(lane_maxabs64<NW>(w));
+        Acc2 tot; double mx;
+        exchange(acc.s, acc.c, m, tot, mx);
+        Scale64 sc; sc.pre = 0; sc.kind = kFast;
+        double hi, lo;
+        tot.split(hi, lo);
+        if (ss_in_range(hi)) {
+          sc.from_ss(hi, lo);
+        } else if (!(mx > 0.0) || !(mx <= DBL_MAX)) {
+          sc.kind = kCopy;
+        } else {                                       // group-uniform slow path
+          sc.kind = kSlow;
+          sc.pre = -ilogb(mx);
+          lane_sumsq64<NW>(w, sc.pre, acc);
+          acc.warp_reduce();
+          double mx2;
+          exchange(acc.s, acc.c, 0.0, tot, mx2);
+          tot.split(hi, lo);
+          sc.from_ss(hi, lo);
+        }
+        lane_apply64<NW>(w, sc);
+      }
+    }
+
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int idx = (j * G + g) * 32 + lane;
+      if (idx < nvec) st_vec<VB, HINT>(dst + (int64_t)idx * VB, &w[j * W]);
+    }
+  }
+}
+
 // ------------------------------------------------------------ general kernel ----
-// Any k, any D, any element-aligned pointers; also the ragged path.  One warp per row, two
-// passes over the row prefix (the second pass re-reads from L1/L2), element-wise coalesced
-// accesses.  k_per_row == nullptr -> every row keeps k; out_offsets == nullptr -> dense.
+// Any k, any D, any element-aligned pointers.  k_per_row == nullptr -> every row keeps k;
+// out_offsets == nullptr -> dense output.
 template <typename T, int MODE>
 __global__ void __launch_bounds__(kThreads)
 rows_general_kernel(const T* __restrict__ in, T* __restrict__ out, int64_t batch, int64_t D,
@@ -289,49 +522,10 @@ rows_general_kernel(const T* __restrict__ in, T* __restrict__ out, int64_t batch
   const int lane = threadIdx.x & 31;
   const int64_t warp = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * kThreads) >> 5;
-
   for (int64_t row = warp; row < batch; row += nwarps) {
     int64_t kr = k_per_row ? (int64_t)k_per_row[row] : k;
     if (kr > D) kr = D;
-    const T* x = in + row * D;
-    T* y = out + (out_offsets ? out_offsets[row] : row * kr);
-
-    if constexpr (MODE == kModeTruncate) {
-      for (int64_t i = lane; i < kr; i += 32) y[i] = x[i];
-    } else if constexpr (sizeof(T) == 4) {
-      double a = 0.0;
-      for (int64_t i = lane; i < kr; i += 32) { const double xv = (double)x[i]; a = fma(xv, xv, a); }
-      Scale32 sc; sc.from_ss(warp_sum(a));
-      if (sc.kind == kCopy) { for (int64_t i = lane; i < kr; i += 32) y[i] = x[i]; }
-      else { for (int64_t i = lane; i < kr; i += 32) y[i] = sc.apply(x[i]); }
-    } else {
-      Acc2 acc; acc.clear();
-      for (int64_t i = lane; i < kr; i += 32) acc.add_square(x[i]);
-      acc.warp_reduce();
-      Scale64 sc; sc.pre = 0;
-      const double ss_hi = acc.s + acc.c;
-      if (ss_in_range(ss_hi)) {
-        sc.kind = kFast;
-        sc.from_ss(ss_hi, (acc.s - ss_hi) + acc.c);
-      } else {
-        double m = 0.0;
-        for (int64_t i = lane; i < kr; i += 32) m = fmax(m, fabs(x[i]));
-        m = warp_max(m);
-        if (!(m > 0.0) || !(m <= DBL_MAX)) {
-          sc.kind = kCopy;
-        } else {
-          sc.kind = kSlow;
-          sc.pre = -ilogb(m);
-          Acc2 a2; a2.clear();
-          for (int64_t i = lane; i < kr; i += 32) a2.add_square(scalbn(x[i], sc.pre));
-          a2.warp_reduce();
-          const double h2 = a2.s + a2.c;
-          sc.from_ss(h2, (a2.s - h2) + a2.c);
-        }
-      }
-      if (sc.kind == kCopy) { for (int64_t i = lane; i < kr; i += 32) y[i] = x[i]; }
-      else { for (int64_t i = lane; i < kr; i += 32) y[i] = sc.apply(x[i]); }
-    }
+    general_row<T, MODE>(in + row * D, out + (out_offsets ? out_offsets[row] : row * kr), kr, lane);
   }
 }
 

@@ -85,6 +85,14 @@ SHAPES = [
     (500, 40, 40, np.float64, 11), (500, 40, 39, np.float64, 11), (500, 4096, 1, np.float32, 11),
     (500, 4, 2, np.float64, 12), (500, 100, 96, np.float32, 12), (333, 1000, 36, np.float32, 12),
     (200, 48, 1000, np.float32, 13), (200, 48, 48, np.float64, 13),         # k >= D
+    # short rows: 8 / 16 lanes per row
+    (4099, 768, 8, np.float32, 14), (4099, 768, 64, np.float32, 14), (4099, 768, 128, np.float32, 14),
+    (4099, 4096, 4, np.float64, 14), (4099, 4096, 32, np.float64, 14), (4099, 4096, 64, np.float64, 14),
+    (4099, 4096, 24, np.float64, 14), (4099, 772, 12, np.float32, 14),        # 16-byte tiles only
+    # several warps per row: 12, 16, 32, 64 KiB prefixes, then beyond
+    (257, 3072, 1536, np.float64, 15), (257, 4096, 4096, np.float32, 15), (129, 4096, 4096, np.float64, 15),
+    (65, 8192, 8192, np.float64, 15), (65, 16384, 16384, np.float32, 15), (33, 20000, 20000, np.float32, 15),
+    (129, 4096, 3000, np.float32, 15), (129, 4096, 1100, np.float64, 15),
 ]
 
 
@@ -119,6 +127,27 @@ def test_random_mantissas_and_scales(oracle, dt):
     xs = (rng.integers(-1000, 1000, size=(64, D)) * tiny).astype(dt)
     got = gu.run_dense(gu.to_dev(xs), k, eg.TRUNCATE_RENORM).cpu().numpy()
     assert_ulp(oracle, got, oracle.renorm_exact(xs, k), what="subnormal rows")
+
+
+@pytest.mark.parametrize("dt", [np.float32, np.float64])
+@pytest.mark.parametrize("k", [8, 16, 64, 2048, 6144])
+def test_mixed_row_kinds_side_by_side(oracle, dt, k):
+    """Neighbouring rows that need different treatment (all zeros, squares overflowing,
+    squares underflowing, ordinary) must not disturb each other: short rows share a warp,
+    long rows share a block."""
+    rng = np.random.default_rng(k)
+    rows, D = 515, 6144
+    fi = np.finfo(dt)
+    kinds = rng.integers(0, 4, size=rows)
+    x = rng.standard_normal((rows, D))
+    x[kinds == 1] *= float(fi.max) / 16
+    x[kinds == 2] *= float(fi.smallest_subnormal) * 64
+    xh = x.astype(dt)
+    xh[kinds == 0, :k] = 0
+    assert np.isfinite(xh).all()
+    got = gu.run_dense(gu.to_dev(xh), k, eg.TRUNCATE_RENORM).cpu().numpy()
+    assert np.isfinite(got).all()
+    assert_ulp(oracle, got, oracle.renorm_exact(xh, k), what=f"mixed kinds k={k}")
 
 
 @pytest.mark.parametrize("dt", [np.float32, np.float64])

@@ -44,22 +44,41 @@ static int g_sms = 148;
 static const char* g_filter = nullptr;
 static bool want(const std::string& n) { return !g_filter || n.find(g_filter) != std::string::npos; }
 
-template <typename T, int NV, int R, int MODE, int MINB>
+template <typename T, int VB, int NV, int R, int MODE, int MINB, int HINT, int L = 32>
 void run_reg(const Shape& s, const void* in, void* out, Timer& tm, int waves = 1) {
   char name[128];
-  snprintf(name, sizeof name, "%s reg<NV=%d,R=%d,mode=%d,minb=%d,w=%d>", s.name, NV, R, MODE, MINB, waves);
+  snprintf(name, sizeof name, "%s reg<VB=%d,NV=%d,R=%d,L=%d,mode=%d,minb=%d,hint=%d,w=%d>", s.name, VB, NV, R, L, MODE, MINB, HINT, waves);
   if (!want(name)) return;
-  auto kern = rows_reg_kernel<T, NV, R, MODE, MINB>;
+  auto kern = rows_reg_kernel<T, VB, NV, R, L, MODE, MINB, HINT, false>;
   int per_sm = 0;
   CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kThreads, 0));
   cudaFuncAttributes fa; CK(cudaFuncGetAttributes(&fa, kern));
-  const int64_t need = (s.rows + kWarpsPerBlock * R - 1) / (kWarpsPerBlock * R);
-  const int grid = (int)std::min<int64_t>(need, (int64_t)g_sms * per_sm * waves);
-  const int nvec = (int)(s.k * s.es / 16);
+  const int64_t rpb = kWarpsPerBlock * R * (32 / L);
+  const int64_t need = (s.rows + rpb - 1) / rpb;
+  const int grid = waves > 0 ? (int)std::min<int64_t>(need, (int64_t)g_sms * per_sm * waves) : (int)need;
+  const int nvec = (int)(s.k * s.es / VB);
+  double ms = tm.ms([&](int) { kern<<<grid, kThreads>>>((const char*)in, (char*)out, s.rows, s.D * s.es, nvec, s.D, nullptr, nullptr); }, 3, 20);
+  CK(cudaGetLastError());
+  double gbs = (double)s.rows * 2 * s.k * s.es / ms / 1e6;
+  printf("%-78s %8.3f ms %8.1f GB/s  regs=%d occ=%d grid=%d\n", name, ms, gbs, fa.numRegs, per_sm, grid);
+}
+
+template <typename T, int VB, int NV, int G, int MODE, int MINB, int HINT>
+void run_coop(const Shape& s, const void* in, void* out, Timer& tm, int waves = 0) {
+  char name[128];
+  snprintf(name, sizeof name, "%s coop<VB=%d,NV=%d,G=%d,mode=%d,minb=%d,hint=%d,w=%d>", s.name, VB, NV, G, MODE, MINB, HINT, waves);
+  if (!want(name)) return;
+  auto kern = rows_coop_kernel<T, VB, NV, G, MODE, MINB, HINT>;
+  int per_sm = 0;
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kThreads, 0));
+  cudaFuncAttributes fa; CK(cudaFuncGetAttributes(&fa, kern));
+  const int64_t need = (s.rows + kWarpsPerBlock / G - 1) / (kWarpsPerBlock / G);
+  const int grid = waves > 0 ? (int)std::min<int64_t>(need, (int64_t)g_sms * per_sm * waves) : (int)need;
+  const int nvec = (int)(s.k * s.es / VB);
   double ms = tm.ms([&](int) { kern<<<grid, kThreads>>>((const char*)in, (char*)out, s.rows, s.D * s.es, nvec); }, 3, 20);
   CK(cudaGetLastError());
   double gbs = (double)s.rows * 2 * s.k * s.es / ms / 1e6;
-  printf("%-64s %8.3f ms %8.1f GB/s  regs=%d occ=%d grid=%d\n", name, ms, gbs, fa.numRegs, per_sm, grid);
+  printf("%-78s %8.3f ms %8.1f GB/s  regs=%d occ=%d grid=%d\n", name, ms, gbs, fa.numRegs, per_sm, grid);
 }
 
 int main(int argc, char** argv) {
@@ -85,50 +104,44 @@ int main(int argc, char** argv) {
   }
 
   std::vector<Shape> shapes = {
-      {"C3f32 1Mx4096->1024", 1048576, 4096, 1024, 4},
+      {"K64f64 2Mx4096->64", 2097152, 4096, 64, 8},
+      {"K32f64 2Mx4096->32", 2097152, 4096, 32, 8},
+      {"K128f32 2Mx768->128", 2097152, 768, 128, 4},
+      {"K64f32 4Mx768->64", 4194304, 768, 64, 4},
       {"C4f32 2Mx3072->256", 2097152, 3072, 256, 4},
-      {"C2x16 1Mx768->256", 1048576, 768, 256, 4},
-      {"C3f64 512Kx4096->1024", 524288, 4096, 1024, 8},
-      {"C5f64 1Mx4096->256", 1048576, 4096, 256, 8},
   };
   for (const Shape& s : shapes) {
-    if (g_filter && !strstr(s.name, g_filter) && !strchr(g_filter, '<') && !strstr(g_filter, "reg")) { /* filter may target variants */ }
     void *in, *out;
     CK(cudaMalloc(&in, (size_t)s.rows * s.D * s.es));
     CK(cudaMalloc(&out, (size_t)s.rows * s.k * s.es));
     if (s.es == 4) fill_kernel<float><<<g_sms * 16, 256>>>((float*)in, 3, 0, s.rows, s.D, s.D, s.D);
     else fill_kernel<double><<<g_sms * 16, 256>>>((double*)in, 3, 0, s.rows, s.D, s.D, s.D);
     CK(cudaDeviceSynchronize());
-    const int nvl = (int)((s.k * s.es / 16 + 31) / 32);
-    if (s.es == 4) {
-      if (nvl == 8) {
-        run_reg<float, 8, 1, 1, 4>(s, in, out, tm);
-        run_reg<float, 8, 1, 1, 3>(s, in, out, tm);
-        run_reg<float, 8, 1, 1, 2>(s, in, out, tm);
-        run_reg<float, 8, 1, 1, 4>(s, in, out, tm, 4);
-        run_reg<float, 8, 1, 0, 4>(s, in, out, tm);
-      } else if (nvl == 2) {
-        run_reg<float, 2, 4, 1, 4>(s, in, out, tm);
-        run_reg<float, 2, 4, 1, 3>(s, in, out, tm);
-        run_reg<float, 2, 2, 1, 4>(s, in, out, tm);
-        run_reg<float, 2, 2, 1, 6>(s, in, out, tm);
-        run_reg<float, 2, 1, 1, 8>(s, in, out, tm);
-        run_reg<float, 2, 8, 1, 2>(s, in, out, tm);
-        run_reg<float, 2, 4, 1, 4>(s, in, out, tm, 4);
-        run_reg<float, 2, 4, 0, 4>(s, in, out, tm);
-      }
-    } else {
-      if (nvl == 16) {
-        run_reg<double, 16, 1, 1, 1>(s, in, out, tm);
-        run_reg<double, 16, 1, 1, 2>(s, in, out, tm);
-        run_reg<float, 16, 1, 0, 2>(s, in, out, tm);
-      } else if (nvl == 4) {
-        run_reg<double, 4, 2, 1, 2>(s, in, out, tm);
-        run_reg<double, 4, 2, 1, 3>(s, in, out, tm);
-        run_reg<double, 4, 1, 1, 4>(s, in, out, tm);
-        run_reg<double, 4, 4, 1, 1>(s, in, out, tm);
-        run_reg<float, 4, 2, 0, 4>(s, in, out, tm);
-      }
+    const int64_t kb = s.k * s.es;
+    if (s.es == 8 && kb == 512) {
+      run_reg<double, 32, 1, 2, 1, 4, 1, 32>(s, in, out, tm, 0);
+      run_reg<double, 32, 1, 2, 1, 4, 1, 16>(s, in, out, tm, 0);
+      run_reg<double, 32, 1, 4, 1, 4, 1, 16>(s, in, out, tm, 0);
+      run_reg<double, 32, 1, 4, 1, 3, 1, 16>(s, in, out, tm, 0);
+      run_reg<float, 32, 1, 4, 0, 4, 1, 16>(s, in, out, tm, 0);
+    } else if (s.es == 8 && kb == 256) {
+      run_reg<double, 32, 1, 2, 1, 4, 1, 16>(s, in, out, tm, 0);
+      run_reg<double, 32, 1, 2, 1, 4, 1, 8>(s, in, out, tm, 0);
+      run_reg<double, 32, 1, 4, 1, 4, 1, 8>(s, in, out, tm, 0);
+      run_reg<float, 32, 1, 4, 0, 4, 1, 8>(s, in, out, tm, 0);
+    } else if (s.es == 4 && kb == 512) {
+      run_reg<float, 32, 1, 4, 1, 4, 1, 32>(s, in, out, tm, 0);
+      run_reg<float, 32, 1, 4, 1, 4, 1, 16>(s, in, out, tm, 0);
+      run_reg<float, 32, 1, 8, 1, 2, 1, 16>(s, in, out, tm, 0);
+      run_reg<float, 32, 1, 4, 0, 4, 1, 16>(s, in, out, tm, 0);
+    } else if (s.es == 4 && kb == 256) {
+      run_reg<float, 32, 1, 4, 1, 4, 1, 16>(s, in, out, tm, 0);
+      run_reg<float, 32, 1, 4, 1, 4, 1, 8>(s, in, out, tm, 0);
+      run_reg<float, 32, 1, 4, 0, 4, 1, 8>(s, in, out, tm, 0);
+    } else if (s.es == 4 && kb == 1024) {
+      run_reg<float, 32, 1, 4, 1, 4, 1, 32>(s, in, out, tm, 0);
+      run_reg<float, 32, 2, 4, 1, 4, 1, 16>(s, in, out, tm, 0);
+      run_reg<float, 32, 2, 2, 1, 4, 1, 16>(s, in, out, tm, 0);
     }
     CK(cudaFree(in)); CK(cudaFree(out));
   }
