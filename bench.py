@@ -170,6 +170,47 @@ def run_reference(args, wl, rank):
 
 
 # ------------------------------------------------------------------ GPU arm ----
+# kernel the library's dispatcher (csrc/etn_api.cu launch_dense) picks per workload
+KERNELS = {
+    "c1": "etn::rows_reg_kernel<double, VB=32, NV=8, R=1, L=32> (8 KiB rows, one warp per row)",
+    "c2": "etn::rows_reg_kernel<float, VB=32, NV=1, R=4, L=32> (1 KiB rows, four rows per warp)",
+    "c3": "etn::rows_reg_kernel<float, VB=32, NV=4, R=1, L=32> (4 KiB rows, one warp per row)",
+    "c3f64": "etn::rows_reg_kernel<double, VB=32, NV=8, R=1, L=32> (8 KiB rows, one warp per row)",
+    "c4": "etn::rows_reg_kernel<float, VB=32, NV=1, R=4, L=32> (1 KiB rows, four rows per warp)",
+}
+
+
+def quick_measure(torch, eg, wl, peak, steps=100, warmup=5):
+    """Device-resident vectors/s and algorithmic GB/s of one workload on the current GPU."""
+    L = eg.lib()
+    dt = NPDT[wl["dtype"]]
+    tdt = torch.float32 if wl["dtype"] == "f32" else torch.float64
+    es = np.dtype(dt).itemsize
+    rows, D, k, code = wl["rows"], wl["D"], wl["k"], eg.dtype_code(dt)
+    per_set = rows * 2 * k * es
+    n_sets = max(1, -(-4 * L2_BYTES // per_set)) if per_set < 4 * L2_BYTES else 1
+    stream = torch.cuda.current_stream().cuda_stream
+    xs, ys = [], []
+    for i in range(n_sets):
+        x = torch.empty((rows, D), dtype=tdt, device="cuda")
+        eg.check(L.etn_fill_synthetic(wl["seed"] + 100 * i, 0, rows, D, D, D, code, x.data_ptr(), stream), "fill")
+        xs.append(x)
+        ys.append(torch.empty((rows, k), dtype=tdt, device="cuda"))
+    for i in range(warmup):
+        eg.check(L.embed_truncate_norm(rows, D, k, code, xs[i % n_sets].data_ptr(), ys[i % n_sets].data_ptr(), stream), "renorm")
+    torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for i in range(steps):
+        eg.check(L.embed_truncate_norm(rows, D, k, code, xs[i % n_sets].data_ptr(), ys[i % n_sets].data_ptr(), stream), "renorm")
+    ev1.record()
+    torch.cuda.synchronize()
+    s_per = ev0.elapsed_time(ev1) * 1e-3 / steps
+    gbs = per_set / s_per / 1e9
+    return {"workload": wl["desc"], "vectors_per_s": rows / s_per, "us_per_launch": s_per * 1e6, "achieved_GBps": gbs,
+            "frac_of_measured_peak": gbs / peak, "buffer_sets": n_sets, "steps": steps}
+
+
 def run_ours(args, wl, rank, local_rank, world):
     import torch
     import torch.distributed as dist
@@ -261,7 +302,7 @@ def run_ours(args, wl, rank, local_rank, world):
         e2e = {"value": world * e_rows * e_steps / float(el.item()), "unit": "vectors/s",
                "h2d_bytes_per_step": e_rows * k * es, "d2h_bytes_per_step": e_rows * k * es,
                "steps": e_steps, "rows_per_gpu": e_rows, "ms_per_step": 1e3 * float(el.item()) / e_steps,
-               "api": "embed_truncate_norm_host (pinned host buffers, prefix-only H2D, 3 staging slots)"}
+               "api": "embed_truncate_norm_host (pinned host buffers, prefix-only 2-D H2D, 4 staging slots of 64 MiB)"}
         del hx, hy
         pin_in.free(); pin_out.free()
         eg.shutdown()
@@ -272,6 +313,20 @@ def run_ours(args, wl, rank, local_rank, world):
         return
 
     peak, peak_src = measured_peak()
+    # the other BASELINE.json shapes, device-resident, for the record (not the bench line)
+    others = None
+    if world == 1 and not args.no_others:
+        del xs, ys, x
+        torch.cuda.empty_cache()
+        others = {}
+        for name in ("c2", "c4", "c3f64", "c1"):
+            if name == args.workload:
+                continue
+            try:
+                others[name] = quick_measure(torch, eg, WORKLOADS[name], peak)
+            except Exception as e:  # noqa: BLE001
+                others[name] = {"error": repr(e)[:200]}
+            torch.cuda.empty_cache()
     avg_launch_s = ms_total * 1e-3 / args.steps
     algo_bytes = rows * 2 * k * es                          # per launch, per GPU
     achieved = algo_bytes / avg_launch_s / 1e9
@@ -290,11 +345,12 @@ def run_ours(args, wl, rank, local_rank, world):
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": ncu_traffic(args.workload), "peak_source": peak_src,
                      "frac_of_8TBps_nominal": achieved / 8000.0,
-                     "algorithmic_bytes_per_launch": algo_bytes, "kernel": "etn::rows_reg_kernel"},
+                     "algorithmic_bytes_per_launch": algo_bytes, "kernel": KERNELS.get(args.workload)},
         "clocks": clocks,
         "e2e": e2e,
         "gpu_launches": args.steps,
         "cpu_baseline": cpu,
+        "other_workloads": others,
     }
     print(json.dumps(line), flush=True)
     if world > 1:
@@ -310,6 +366,7 @@ def main():
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-others", action="store_true", help="skip the informational runs of the other shapes")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

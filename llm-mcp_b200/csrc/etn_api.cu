@@ -175,8 +175,13 @@ int run_dense(int64_t batch, int64_t D, int64_t k, int dtype, int mode, const vo
 }
 
 // --------------------------------------------------------------- host path ----
-constexpr int kSlots = 3;                          // chunks in flight per device
-constexpr size_t kSlotBytes = 32u << 20;           // staging per slot (prefix bytes)
+// Measured on the B200 box (profiles/r01_pcie_study.txt): DMA moves 55.6 GB/s H2D, 57.3 GB/s
+// D2H, 50 GB/s each way when both run; a prefix-only 2-D copy (4 KiB of every 16 KiB) is as
+// fast as a contiguous one; the kernels reading and writing pinned host memory directly
+// reach 40 GB/s each way.  Hence staged DMA, both directions kept busy at once.
+constexpr int kSlots = 4;                          // chunks in flight per device
+constexpr size_t kSlotBytes = 64u << 20;           // staging per slot (prefix bytes)
+constexpr int64_t kMinChunkBytes = 512 << 10;      // below this a chunk is all launch latency
 
 struct DevCtx {
   int dev = -1;
@@ -202,7 +207,7 @@ void destroy_ctx(DevCtx* c) {
 
 // Processes rows [0, rows) of one device's block.  host_in/host_out already point at the
 // block.  Every chunk runs H2D -> kernel (in place on the dense staging tile) -> D2H on its
-// slot's stream; the three slots keep both copy engines and the SMs busy at once.
+// slot's stream; the slots keep both copy engines and the SMs busy at once.
 int run_block(DevCtx* c, int64_t rows, int64_t D, int64_t kk, int dtype, int mode,
               const char* host_in, int64_t in_pitch, char* host_out) {
   std::lock_guard<std::mutex> lock(c->mu);
@@ -212,6 +217,10 @@ int run_block(DevCtx* c, int64_t rows, int64_t D, int64_t kk, int dtype, int mod
   const int64_t k_bytes = kk * es;
   int64_t chunk_rows = (int64_t)(kSlotBytes / (size_t)k_bytes);
   if (chunk_rows < 1) return ETN_ERR_SHAPE;        // one row prefix larger than a slot
+  // a request-sized batch is cut into ~2*kSlots chunks so its D2H overlaps its own H2D
+  const int64_t split = (rows + 2 * kSlots - 1) / (2 * kSlots);
+  const int64_t floor_rows = std::max<int64_t>(1, kMinChunkBytes / k_bytes);
+  chunk_rows = std::min(chunk_rows, std::max(split, floor_rows));
   int rc = 0;
   int64_t done = 0;
   for (int64_t ci = 0; done < rows && rc == 0; ++ci) {

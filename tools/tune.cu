@@ -81,12 +81,77 @@ void run_coop(const Shape& s, const void* in, void* out, Timer& tm, int waves = 
   printf("%-78s %8.3f ms %8.1f GB/s  regs=%d occ=%d grid=%d\n", name, ms, gbs, fa.numRegs, per_sm, grid);
 }
 
+// PCIe study for the host path: DMA ceilings, prefix-only 2-D DMA, and the kernels reading and
+// writing pinned host memory directly (zero copy).  C3 slice: rows x 4096 f32 -> 1024.
+static void pcie_study(Timer& tm) {
+  const int64_t rows = 262144, D = 4096, k = 1024, es = 4;
+  const size_t in_bytes = (size_t)rows * D * es, pre_bytes = (size_t)rows * k * es;
+  char *hin, *hout, *din, *dout;
+  CK(cudaHostAlloc(&hin, in_bytes, cudaHostAllocPortable));
+  CK(cudaHostAlloc(&hout, pre_bytes, cudaHostAllocPortable));
+  CK(cudaMalloc(&din, in_bytes)); CK(cudaMalloc(&dout, pre_bytes));
+  fill_kernel<float><<<g_sms * 16, 256>>>((float*)din, 3, 0, rows, D, D, D);
+  CK(cudaMemcpy(hin, din, in_bytes, cudaMemcpyDeviceToHost));
+  cudaStream_t s1, s2; CK(cudaStreamCreate(&s1)); CK(cudaStreamCreate(&s2));
+  auto rep = [&](const char* nm, double ms, double bytes) { printf("%-64s %8.3f ms %8.1f GB/s\n", nm, ms, bytes / ms / 1e6); };
+  double ms;
+  ms = tm.ms([&](int) { CK(cudaMemcpyAsync(din, hin, pre_bytes, cudaMemcpyHostToDevice)); }, 1, 5);
+  rep("pcie H2D 1 GiB contiguous", ms, pre_bytes);
+  ms = tm.ms([&](int) { CK(cudaMemcpyAsync(hout, dout, pre_bytes, cudaMemcpyDeviceToHost)); }, 1, 5);
+  rep("pcie D2H 1 GiB contiguous", ms, pre_bytes);
+  ms = tm.ms([&](int) { CK(cudaMemcpy2DAsync(din, k * es, hin, D * es, k * es, rows, cudaMemcpyHostToDevice)); }, 1, 5);
+  rep("pcie H2D 2-D prefix (4 KiB of every 16 KiB)", ms, pre_bytes);
+  {
+    cudaEvent_t a, b, c; CK(cudaEventCreate(&a)); CK(cudaEventCreate(&b)); CK(cudaEventCreate(&c));
+    CK(cudaDeviceSynchronize());
+    CK(cudaEventRecord(a, s1)); CK(cudaStreamWaitEvent(s2, a));
+    for (int i = 0; i < 5; ++i) {
+      CK(cudaMemcpyAsync(din, hin, pre_bytes, cudaMemcpyHostToDevice, s1));
+      CK(cudaMemcpyAsync(hout, dout, pre_bytes, cudaMemcpyDeviceToHost, s2));
+    }
+    CK(cudaEventRecord(c, s2)); CK(cudaStreamWaitEvent(s1, c)); CK(cudaEventRecord(b, s1));
+    CK(cudaEventSynchronize(b));
+    float t; CK(cudaEventElapsedTime(&t, a, b));
+    rep("pcie H2D + D2H concurrently (each direction)", t / 5, pre_bytes);
+  }
+  const int nvec = (int)(k * es / 32);
+  auto kern = rows_reg_kernel<float, 32, 4, 1, 32, 1, 4, 1, false>;
+  const int grid = (int)((rows + 7) / 8);
+  ms = tm.ms([&](int) { kern<<<grid, kThreads>>>(hin, hout, rows, D * es, nvec, D, nullptr, nullptr); }, 1, 5);
+  rep("zero-copy kernel: host in -> host out (per direction)", ms, pre_bytes);
+  ms = tm.ms([&](int) { kern<<<grid, kThreads>>>(hin, dout, rows, D * es, nvec, D, nullptr, nullptr); }, 1, 5);
+  rep("zero-copy kernel: host in -> device out", ms, pre_bytes);
+  ms = tm.ms([&](int) { kern<<<grid, kThreads>>>(din, hout, rows, D * es, nvec, D, nullptr, nullptr); }, 1, 5);
+  rep("zero-copy kernel: device in -> host out", ms, pre_bytes);
+  auto kern16 = rows_reg_kernel<float, 16, 8, 1, 32, 1, 4, 0, false>;
+  ms = tm.ms([&](int) { kern16<<<grid, kThreads>>>(hin, hout, rows, D * es, (int)(k * es / 16), D, nullptr, nullptr); }, 1, 5);
+  rep("zero-copy kernel 128-bit: host in -> host out", ms, pre_bytes);
+  for (int g : {148, 296, 592, 2368}) {
+    char nm[96]; snprintf(nm, sizeof nm, "zero-copy kernel grid=%d: host in -> host out", g);
+    ms = tm.ms([&](int) { kern<<<g, kThreads>>>(hin, hout, rows, D * es, nvec, D, nullptr, nullptr); }, 1, 5);
+    rep(nm, ms, pre_bytes);
+  }
+  // small request latency: C1 1024 x 4096 f64 -> 1024 (8 MiB each way)
+  {
+    auto k64 = rows_reg_kernel<double, 32, 8, 1, 32, 1, 2, 1, false>;
+    ms = tm.ms([&](int) { k64<<<128, kThreads>>>(hin, hout, 1024, 4096 * 8, 256, 4096, nullptr, nullptr); }, 2, 20);
+    rep("C1 zero-copy kernel host->host (8 MiB each way)", ms, 8.0 * 1048576);
+    ms = tm.ms([&](int) {
+      CK(cudaMemcpy2DAsync(din, 8192, hin, 32768, 8192, 1024, cudaMemcpyHostToDevice));
+      k64<<<128, kThreads>>>(din, dout, 1024, 8192, 256, 1024, nullptr, nullptr);
+      CK(cudaMemcpyAsync(hout, dout, 8388608, cudaMemcpyDeviceToHost)); }, 2, 20);
+    rep("C1 staged H2D(2-D) + kernel + D2H (8 MiB each way)", ms, 8.0 * 1048576);
+  }
+  CK(cudaFreeHost(hin)); CK(cudaFreeHost(hout)); CK(cudaFree(din)); CK(cudaFree(dout));
+}
+
 int main(int argc, char** argv) {
   if (argc > 1) g_filter = argv[1];
   cudaDeviceProp p; CK(cudaGetDeviceProperties(&p, 0));
   g_sms = p.multiProcessorCount;
   printf("device %s, %d SMs, L2 %d MiB\n", p.name, g_sms, p.l2CacheSize >> 20);
   Timer tm;
+  if (g_filter && !strcmp(g_filter, "pcie")) { pcie_study(tm); return 0; }
 
   // ceilings: 4 GiB read + 4 GiB written
   {
