@@ -236,3 +236,32 @@ def truncate_embeddings(result: Any, dims: int, renorm: bool | None = None) -> d
         stats["gpu_vectors"] += n
         stats["launch_groups"] += 1
     return stats
+
+
+# ----------------------------------------------------------------- row sharding ----
+def shard_rows(batch: int, world: int) -> list[tuple[int, int]]:
+    """Contiguous row blocks, the split embed_truncate_norm_host uses: shard g gets rows
+    [g*ceil(B/G), min(B, (g+1)*ceil(B/G))).  Rows are independent (each vector is handled on
+    its own at handlers.go:2068-2076), so shards never exchange data."""
+    if world < 1 or batch < 0:
+        raise ValueError("world >= 1 and batch >= 0")
+    per = -(-batch // world) if batch else 0
+    return [(min(batch, g * per), min(batch, (g + 1) * per)) for g in range(world)]
+
+
+def shard_ragged(k_per_row, D: int, world: int) -> list[tuple[int, int]]:
+    """Contiguous row ranges of a ragged batch balanced by bytes moved (sum of min(k, D)),
+    not by row count: the cost of a row is proportional to its k."""
+    kk = np.minimum(np.asarray(k_per_row, dtype=np.int64), D)
+    if world < 1:
+        raise ValueError("world >= 1")
+    n = len(kk)
+    csum = np.concatenate([[0], np.cumsum(kk)])
+    total = int(csum[-1])
+    cuts = [0]
+    for g in range(1, world):
+        target = total * g / world
+        cuts.append(int(np.searchsorted(csum, target, side="left")))
+    cuts.append(n)
+    cuts = np.maximum.accumulate(np.minimum(cuts, n))
+    return [(int(cuts[g]), int(cuts[g + 1])) for g in range(world)]

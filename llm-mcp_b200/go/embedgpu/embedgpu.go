@@ -1,0 +1,152 @@
+// Package embedgpu binds libembed_truncate_norm.so (include/embed_truncate_norm.h) for
+// LLM-MCP's core.  It is the cgo package INTEGRATION.md proposes as
+// core/internal/embedgpu; TruncateEmbeddings is a drop-in for the private function
+// truncateEmbeddings(result map[string]any, dims int) at core/internal/api/handlers.go:2062-2078.
+//
+// NOT COMPILED IN THIS REPOSITORY: the build image has no Go toolchain (SURVEY.md F4).
+// The Python mirror llm-mcp_b200/embedgpu.py implements the same logic over the same C-ABI
+// and is what the tests exercise.  Building this needs CGO_ENABLED=1 (the reference builds
+// with CGO_ENABLED=0, core/Dockerfile:6) and a glibc base image with the NVIDIA driver.
+package embedgpu
+
+/*
+#cgo CFLAGS: -I${SRCDIR}/../../../include
+#cgo LDFLAGS: -L${SRCDIR}/../.. -lembed_truncate_norm
+#include <stdlib.h>
+#include "embed_truncate_norm.h"
+*/
+import "C"
+
+import (
+	"fmt"
+	"log/slog"
+	"os"
+	"strconv"
+	"sync"
+	"unsafe"
+)
+
+// Init binds the visible GPUs (call once from main, next to api.New at
+// core/cmd/core/main.go:49-51).  A non-nil error means "serve with the reference reslice".
+func Init() error {
+	if rc := C.etn_init(nil, 0); rc != 0 {
+		return fmt.Errorf("etn_init: %s (%d)", C.GoString(C.etn_strerror(rc)), int(rc))
+	}
+	ready = true
+	return nil
+}
+
+// Shutdown releases streams and staging buffers (main.go:118-122).
+func Shutdown() { ready = false; C.etn_shutdown() }
+
+var ready bool
+
+// RenormEnabled reports EMBED_RENORMALIZE=1, read on every call like config.GetenvInt does
+// (core/internal/config/config.go:17-24).  Default off: the reference only truncates.
+func RenormEnabled() bool {
+	n, err := strconv.Atoi(os.Getenv("EMBED_RENORMALIZE"))
+	return err == nil && n == 1
+}
+
+// pinned is a reusable pair of page-locked buffers; handlers run concurrently
+// (one goroutine per connection), so they come from a pool.
+type pinned struct {
+	in, out   unsafe.Pointer
+	inN, outN int // capacity in float64 elements
+}
+
+var pool = sync.Pool{New: func() any { return &pinned{} }}
+
+func (p *pinned) ensure(inN, outN int) bool {
+	if inN > p.inN {
+		C.etn_free_pinned(p.in)
+		p.in, p.inN = C.etn_alloc_pinned(C.size_t(inN*8)), inN
+	}
+	if outN > p.outN {
+		C.etn_free_pinned(p.out)
+		p.out, p.outN = C.etn_alloc_pinned(C.size_t(outN*8)), outN
+	}
+	return p.in != nil && p.out != nil
+}
+
+// reslice is the reference behaviour, kept as the fallback (handlers.go:2073-2076).
+func reslice(m map[string]any, emb []any, dims int) { m["embedding"] = emb[:dims] }
+
+// TruncateEmbeddings keeps the first dims components of every embedding of an OpenAI-format
+// response and, when EMBED_RENORMALIZE=1, L2-renormalises them on the GPU.  Same skips as
+// the reference: data not a list, items not maps, embeddings that are not lists (base64,
+// null), vectors with len <= dims.  Vectors are packed per source length into pinned
+// memory (no Go pointer is ever handed to C) and each group is one
+// embed_truncate_norm_host call.  Any error falls back to the reslice, so the request
+// still succeeds (the cloud branch has no retry, handlers.go:1881-1886).
+func TruncateEmbeddings(result map[string]any, dims int) {
+	data, ok := result["data"].([]any)
+	if !ok || dims <= 0 {
+		return
+	}
+	mode := C.int(C.ETN_TRUNCATE)
+	if RenormEnabled() {
+		mode = C.ETN_TRUNCATE_RENORM
+	}
+	groups := map[int][]map[string]any{}
+	for _, item := range data {
+		m, ok := item.(map[string]any)
+		if !ok {
+			continue
+		}
+		emb, ok := m["embedding"].([]any)
+		if !ok || len(emb) <= dims {
+			continue
+		}
+		if !ready || mode == C.ETN_TRUNCATE || !allFloat64(emb) {
+			reslice(m, emb, dims) // truncation alone needs no arithmetic: O(1), as in the reference
+			continue
+		}
+		groups[len(emb)] = append(groups[len(emb)], m)
+	}
+	for D, items := range groups {
+		n := len(items)
+		p := pool.Get().(*pinned)
+		if !p.ensure(n*D, n*dims) {
+			pool.Put(p)
+			for _, m := range items {
+				reslice(m, m["embedding"].([]any), dims)
+			}
+			continue
+		}
+		in := unsafe.Slice((*float64)(p.in), n*D)
+		for r, m := range items {
+			for c, v := range m["embedding"].([]any) {
+				in[r*D+c] = v.(float64)
+			}
+		}
+		rc := C.embed_truncate_norm_host(C.int64_t(n), C.int64_t(D), C.int64_t(dims), C.ETN_F64, mode,
+			p.in, 0, p.out, 0)
+		if rc != 0 {
+			slog.Error("embedgpu", "error", C.GoString(C.etn_strerror(rc)), "code", int(rc))
+			for _, m := range items {
+				reslice(m, m["embedding"].([]any), dims)
+			}
+			pool.Put(p)
+			continue
+		}
+		out := unsafe.Slice((*float64)(p.out), n*dims)
+		for r, m := range items {
+			emb := m["embedding"].([]any)[:dims] // reuse the backing array, as the reslice does
+			for c := range emb {
+				emb[c] = out[r*dims+c]
+			}
+			m["embedding"] = emb
+		}
+		pool.Put(p)
+	}
+}
+
+func allFloat64(emb []any) bool {
+	for _, v := range emb {
+		if _, ok := v.(float64); !ok {
+			return false
+		}
+	}
+	return true
+}
