@@ -65,6 +65,7 @@ extern "C" {
 #define ETN_ERR_ALIGN (-4)    /* pointer not aligned to the element size */
 #define ETN_ERR_NOT_INIT (-5) /* host path used before etn_init */
 #define ETN_ERR_DEVICE (-6)   /* bad device list / n_devices */
+#define ETN_ERR_TOO_LARGE (-7) /* more than ETN_STATIC_STAGE_BYTES asked of the _static entry point */
 
 /* Library version (ETN_VERSION of the build).  No reference counterpart. */
 ETN_API int etn_version(void);
@@ -126,6 +127,39 @@ ETN_API void etn_free_pinned(void *p);
 ETN_API int embed_truncate_norm_host(int64_t batch, int64_t D, int64_t k, int dtype, int mode,
                              const void *host_in, int64_t in_pitch_bytes, void *host_out,
                              int n_devices);
+
+/* Size of the staging array built into the library image: 16 MiB of device memory on every
+ * GPU that loads the library, held until the process exits. */
+#define ETN_STATIC_STAGE_BYTES (16u << 20)
+
+/* embed_truncate_norm_host for callers that cannot allocate device memory.  It has no
+ * counterpart in the reference.
+ *
+ * Who needs it: embed_truncate_norm_host stages through buffers that etn_init obtains with
+ * cudaMalloc.  A llmcore process that shares its GPU with a model server (Ollama, vLLM) often
+ * finds the device already filled by that server's up-front reservation, so a 256 MiB
+ * cudaMalloc at start-up or request time fails; a short-lived helper (a health probe such as
+ * POST /v1/debug/test, a CLI check) does not want etn_init's set-up at all; and a handler on a
+ * latency budget should not be exposed to an allocator call that may block behind other
+ * work on the device.  This entry point asks no allocator for anything: not cudaMalloc, not
+ * cudaFree, not a stream or event, nothing from any library.  Its device staging is an array
+ * compiled into the library.  It needs no etn_init.
+ *
+ * Same arguments and results as embed_truncate_norm_host, except: it runs on the calling
+ * thread's current device only, on `stream` (NULL = the legacy default stream), and the
+ * kept prefixes must fit the array: batch * min(k, D) * element size <=
+ * ETN_STATIC_STAGE_BYTES, otherwise ETN_ERR_TOO_LARGE and nothing is done (C1, 1024 x 1024
+ * float64, is 8 MiB).  Synchronous: it returns after `stream` has drained.
+ *
+ * The first call on each device looks up the array's device address (set-up, once per
+ * device); make that first call before starting any stream capture on that device.
+ * All calls on a device share the one array, which keeps whatever the previous call left
+ * in it; nothing in it has to be zero, since each call first overwrites the region it then
+ * uses.  Two calls overlapping on the GPU would race on it, so the library holds a per-device
+ * lock for the length of a call and concurrent callers queue. */
+ETN_API int embed_truncate_norm_host_static(int64_t batch, int64_t D, int64_t k, int dtype, int mode,
+                                            const void *host_in, int64_t in_pitch_bytes,
+                                            void *host_out, void *stream);
 
 /* ---- bench/test utility ---- */
 

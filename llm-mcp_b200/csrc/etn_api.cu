@@ -254,6 +254,20 @@ int run_block(DevCtx* c, int64_t rows, int64_t D, int64_t kk, int dtype, int mod
 
 }  // namespace
 
+// ------------------------------------------------- built-in staging array ----
+// Device staging for embed_truncate_norm_host_static: reserved in the module image, so it
+// exists from the moment the library is loaded on a GPU until the process exits and no
+// allocator is ever involved.  In host code `g_static_stage` is only a handle for the
+// symbol, not a device address; the address a kernel or a copy can use is looked up once
+// per device with cudaGetSymbolAddress, with that device current.
+static __device__ __align__(256) unsigned char g_static_stage[ETN_STATIC_STAGE_BYTES];
+
+struct StaticStage {
+  std::mutex mu;            // set-up, and one call at a time on the array
+  void* ptr = nullptr;      // device address of g_static_stage on this device
+};
+static StaticStage g_static[kMaxDevices];
+
 // =============================================================== C-ABI ======
 extern "C" {
 
@@ -268,6 +282,7 @@ const char* etn_strerror(int code) {
     case ETN_ERR_ALIGN: return "pointer not aligned to the element size";
     case ETN_ERR_NOT_INIT: return "etn_init has not been called";
     case ETN_ERR_DEVICE: return "bad device list";
+    case ETN_ERR_TOO_LARGE: return "batch does not fit the built-in staging array (ETN_STATIC_STAGE_BYTES)";
     default: break;
   }
   if (code > 0) return cudaGetErrorString((cudaError_t)code);
@@ -417,6 +432,58 @@ int embed_truncate_norm_host(int64_t batch, int64_t D, int64_t k, int dtype, int
   if (have_prev) cudaSetDevice(prev);
   for (int rc : rcs) if (rc) return rc;
   return ETN_OK;
+}
+
+int embed_truncate_norm_host_static(int64_t batch, int64_t D, int64_t k, int dtype, int mode,
+                                    const void* host_in, int64_t in_pitch_bytes, void* host_out,
+                                    void* stream) {
+  if ((dtype != ETN_F32 && dtype != ETN_F64) || (mode != ETN_TRUNCATE && mode != ETN_TRUNCATE_RENORM))
+    return ETN_ERR_ENUM;
+  if (batch < 0 || D <= 0 || k <= 0) return ETN_ERR_SHAPE;
+  const int64_t es = dtype == ETN_F32 ? 4 : 8;
+  if (in_pitch_bytes == 0) in_pitch_bytes = D * es;
+  if (in_pitch_bytes < D * es || in_pitch_bytes % es != 0) return ETN_ERR_SHAPE;
+  if (batch == 0) return ETN_OK;
+  if (!host_in || !host_out) return ETN_ERR_NULL;
+  if (!aligned_to(host_in, (size_t)es) || !aligned_to(host_out, (size_t)es)) return ETN_ERR_ALIGN;
+  const int64_t kk = std::min(k, D);
+  const int64_t k_bytes = kk * es;
+  if (k_bytes > (int64_t)ETN_STATIC_STAGE_BYTES || batch > (int64_t)ETN_STATIC_STAGE_BYTES / k_bytes)
+    return ETN_ERR_TOO_LARGE;
+
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= kMaxDevices) return ETN_ERR_DEVICE;
+  StaticStage& st = g_static[dev];
+  // Held until the stream has drained: every call on this device uses the same array.
+  std::lock_guard<std::mutex> lock(st.mu);
+  if (!st.ptr) {                                    // first call on this device: set-up
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_static_stage);
+    if (e != cudaSuccess) return (int)e;
+    st.ptr = p;
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t bytes = (size_t)(batch * k_bytes);
+  // Nothing in the array has to start at zero: the copy below overwrites exactly the
+  // [batch x kk] region that the kernel then reads and rewrites in place.
+  if (in_pitch_bytes == k_bytes) {
+    e = cudaMemcpyAsync(st.ptr, host_in, bytes, cudaMemcpyHostToDevice, s);
+  } else {
+    e = cudaMemcpy2DAsync(st.ptr, (size_t)k_bytes, host_in, (size_t)in_pitch_bytes, (size_t)k_bytes,
+                          (size_t)batch, cudaMemcpyHostToDevice, s);
+  }
+  if (e != cudaSuccess) return (int)e;
+  int rc = 0;
+  if (mode == ETN_TRUNCATE_RENORM) rc = run_dense(batch, kk, kk, dtype, mode, st.ptr, st.ptr, s);
+  if (rc == 0) {
+    e = cudaMemcpyAsync(host_out, st.ptr, bytes, cudaMemcpyDeviceToHost, s);
+    if (e != cudaSuccess) rc = (int)e;
+  }
+  e = cudaStreamSynchronize(s);
+  if (e != cudaSuccess && rc == 0) rc = (int)e;
+  return rc;
 }
 
 int etn_fill_synthetic(uint64_t seed, int64_t row0, int64_t rows, int64_t D, int64_t ncols,

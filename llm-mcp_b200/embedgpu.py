@@ -27,12 +27,14 @@ LIB_PATH = os.path.join(_PKG, "libembed_truncate_norm.so")
 
 F32, F64 = 0, 1
 TRUNCATE, TRUNCATE_RENORM = 0, 1
-ERR_NULL, ERR_SHAPE, ERR_ENUM, ERR_ALIGN, ERR_NOT_INIT, ERR_DEVICE = -1, -2, -3, -4, -5, -6
+ERR_NULL, ERR_SHAPE, ERR_ENUM, ERR_ALIGN, ERR_NOT_INIT, ERR_DEVICE, ERR_TOO_LARGE = -1, -2, -3, -4, -5, -6, -7
+STATIC_STAGE_BYTES = 16 << 20
 
 EXPORTS = (
     "etn_version", "etn_strerror", "embed_truncate_norm", "embed_truncate",
     "embed_truncate_norm_ragged", "etn_init", "etn_shutdown", "etn_device_count",
     "etn_alloc_pinned", "etn_free_pinned", "embed_truncate_norm_host", "etn_fill_synthetic",
+    "embed_truncate_norm_host_static",
 )
 
 
@@ -70,6 +72,7 @@ def lib() -> ctypes.CDLL:
         L.etn_free_pinned.restype = None
         L.embed_truncate_norm_host.argtypes = [i64, i64, i64, ci, ci, vp, i64, vp, ci]
         L.etn_fill_synthetic.argtypes = [ctypes.c_uint64, i64, i64, i64, i64, i64, ci, vp, vp]
+        L.embed_truncate_norm_host_static.argtypes = [i64, i64, i64, ci, ci, vp, i64, vp, vp]
         _lib = L
     return _lib
 
