@@ -116,3 +116,18 @@ def test_mirror_dims_not_positive_is_noop(oracle):
     for dims in (0, -3):                      # handlers.go:1891: the op runs only when dims > 0
         eg.truncate_embeddings(r, dims)
         assert r == keep
+
+
+def test_host_path_row_sharded_over_devices(oracle):
+    """n_devices > 1: contiguous row blocks, one host thread and its own streams per device,
+    no exchange between devices."""
+    n = eg.lib().etn_device_count()
+    if n < 2:
+        pytest.skip("one device visible")
+    rows, D, k = 100003, 1024, 256
+    xh = oracle.fill(9, rows, D, np.float32)
+    want = oracle.renorm_exact(xh, k)
+    for nd in sorted({2, n}):
+        got = eg.truncate_norm_host(xh, k, eg.TRUNCATE_RENORM, n_devices=nd)
+        _ulp(oracle, got, want)
+    assert eg.lib().embed_truncate_norm_host(4, 8, 4, eg.F32, 1, xh.ctypes.data, 0, xh.ctypes.data, n + 1) == eg.ERR_DEVICE
