@@ -10,6 +10,7 @@
 #include "etn_kernels.cuh"
 
 #include <algorithm>
+#include <cstdlib>
 #include <atomic>
 #include <mutex>
 #include <thread>
@@ -59,6 +60,30 @@ int grid_for(K kernel, int64_t blocks_needed, int waves, int* grid) {
 }
 
 // ------------------------------------------------------------- launchers ----
+// Programmatic dependent launch: a launch may be scheduled while the previous kernel of the
+// stream drains, and its blocks wait in griddepcontrol.wait (first thing every kernel does)
+// until that kernel has completed and its writes are visible.  This hides the 3-5 us between
+// back-to-back request-sized launches (C1: 8 us, C2: 20 us of work).  ETN_PDL=0 turns it off.
+bool pdl_enabled() {
+  static const bool on = [] { const char* v = getenv("ETN_PDL"); return !(v && v[0] == '0'); }();
+  return on;
+}
+
+template <typename... KArgs, typename... Args>
+int launch_kernel(void (*kern)(KArgs...), int grid, cudaStream_t s, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return (int)cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 // MINB = resident blocks per SM the register allocation is held to.
 template <typename T, int VB, int NV, int R, int L, int MODE, int MINB, bool RAGGED>
 int launch_reg(const void* in, void* out, int64_t batch, int64_t in_pitch, int nvec, int64_t D,
@@ -67,8 +92,7 @@ int launch_reg(const void* in, void* out, int64_t batch, int64_t in_pitch, int n
   int grid = 0;
   const int64_t rows_per_block = (int64_t)kWarpsPerBlock * R * (32 / L);
   if (int rc = grid_for(kern, (batch + rows_per_block - 1) / rows_per_block, waves, &grid)) return rc;
-  kern<<<grid, kThreads, 0, s>>>((const char*)in, (char*)out, batch, in_pitch, nvec, D, k_per_row, out_offsets);
-  return (int)cudaGetLastError();
+  return launch_kernel(kern, grid, s, (const char*)in, (char*)out, batch, in_pitch, nvec, D, k_per_row, out_offsets);
 }
 
 template <typename T, int VB, int NV, int G, int MODE, int MINB>
@@ -77,8 +101,48 @@ int launch_coop(const void* in, void* out, int64_t batch, int64_t in_pitch, int 
   int grid = 0;
   const int64_t rows_per_block = kWarpsPerBlock / G;
   if (int rc = grid_for(kern, (batch + rows_per_block - 1) / rows_per_block, 0, &grid)) return rc;
-  kern<<<grid, kThreads, 0, s>>>((const char*)in, (char*)out, batch, in_pitch, nvec);
-  return (int)cudaGetLastError();
+  return launch_kernel(kern, grid, s, (const char*)in, (char*)out, batch, in_pitch, nvec);
+}
+
+// Bulk-async (TMA) ring kernel: 4 warps per block, each with its own S-slot ring of row
+// prefixes in shared memory; every warp owns `rpw` consecutive rows.
+template <typename T, int NV16, int S, int MODE, bool RAGGED>
+int launch_bulk(const void* in, void* out, int64_t batch, int64_t in_pitch, int nvec16, int rpw,
+                int64_t D, const int32_t* k_per_row, const int64_t* out_offsets, cudaStream_t s) {
+  constexpr int NCW = 4;
+  constexpr size_t smem = (size_t)NCW * S * NV16 * 512 + (size_t)NCW * S * 8;
+  auto kern = rows_bulk_kernel<T, NV16, S, NCW, MODE, RAGGED>;
+  if (smem > 48 * 1024) {                              // opt in to large dynamic shared memory once per device
+    static std::atomic<uint64_t> done{0};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    const uint64_t bit = 1ull << (dev & 63);
+    if (!(done.load(std::memory_order_acquire) & bit)) {
+      e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return (int)e;
+      done.fetch_or(bit, std::memory_order_release);
+    }
+  }
+  {  // request-sized batches: fewer rows per warp, so that every SM still gets a few blocks
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) sm_count(dev, &sms);
+    rpw = (int)std::max<int64_t>(1, std::min<int64_t>(rpw, batch / ((int64_t)NCW * sms * 2)));
+  }
+  const int64_t rows_per_block = (int64_t)NCW * rpw;
+  const int64_t blocks = std::min<int64_t>((batch + rows_per_block - 1) / rows_per_block, (int64_t)1 << 30);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)std::max<int64_t>(blocks, 1));
+  cfg.blockDim = dim3(NCW * 32);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return (int)cudaLaunchKernelEx(&cfg, kern, (const char*)in, (char*)out, batch, in_pitch, nvec16, rpw, D,
+                                 k_per_row, out_offsets);
 }
 
 template <typename T, int MODE>
@@ -87,8 +151,7 @@ int launch_general(const void* in, void* out, int64_t batch, int64_t D, int64_t 
   auto kern = rows_general_kernel<T, MODE>;
   int grid = 0;
   if (int rc = grid_for(kern, (batch + kWarpsPerBlock - 1) / kWarpsPerBlock, 0, &grid)) return rc;
-  kern<<<grid, kThreads, 0, s>>>((const T*)in, (T*)out, batch, D, k, k_per_row, out_offsets);
-  return (int)cudaGetLastError();
+  return launch_kernel(kern, grid, s, (const T*)in, (T*)out, batch, D, k, k_per_row, out_offsets);
 }
 
 // Dense rows.  Kernel choice by prefix size and alignment:
@@ -107,6 +170,21 @@ int launch_dense(const void* in, void* out, int64_t batch, int64_t D, int64_t kk
   const int64_t in_pitch = D * (int64_t)sizeof(T);
   const int64_t k_bytes = kk * (int64_t)sizeof(T);
   const int W = 0;                                                  // one row group per warp
+  if constexpr (heavy) {
+    // float64 renorm: the reduction is long enough to expose memory latency in the register
+    // kernels (5.5-5.8 TB/s sustained); staging rows through the bulk-async ring keeps
+    // 6.7-6.8 TB/s at every size from 1 to 8 KiB (profiles/r01_tune_bulk.txt).
+    if (aligned_to(in, 16) && aligned_to(out, 16) && in_pitch % 16 == 0 && k_bytes % 16 == 0 &&
+        k_bytes > 512 && k_bytes <= 8192) {
+      const int nvec16 = (int)(k_bytes / 16);
+      const int nv = (nvec16 + 31) / 32;
+      if (nv <= 2)  return launch_bulk<T, 2, 4, MODE, false>(in, out, batch, in_pitch, nvec16, 8, D, nullptr, nullptr, s);
+      if (nv <= 4)  return launch_bulk<T, 4, 2, MODE, false>(in, out, batch, in_pitch, nvec16, 8, D, nullptr, nullptr, s);
+      if (nv <= 8)  return launch_bulk<T, 8, 2, MODE, false>(in, out, batch, in_pitch, nvec16, 4, D, nullptr, nullptr, s);
+      if (nv <= 12) return launch_bulk<T, 12, 2, MODE, false>(in, out, batch, in_pitch, nvec16, 4, D, nullptr, nullptr, s);
+      return launch_bulk<T, 16, 2, MODE, false>(in, out, batch, in_pitch, nvec16, 4, D, nullptr, nullptr, s);
+    }
+  }
   if (aligned_to(in, 32) && aligned_to(out, 32) && in_pitch % 32 == 0 && k_bytes % 32 == 0 &&
       k_bytes <= 64 * 1024) {
     const int nvec = (int)(k_bytes / 32);
@@ -141,15 +219,15 @@ int launch_dense(const void* in, void* out, int64_t batch, int64_t D, int64_t kk
   return launch_general<T, MODE>(in, out, batch, D, kk, nullptr, nullptr, s);
 }
 
-// Ragged rows: a warp per row with room for 8 KiB of prefix in registers when the input is
-// 32-byte tileable (rows that are not, or are longer, fall back inside the kernel).
+// Ragged rows: every row prefix is one bulk-async copy of its own length into a warp's ring
+// (8 KiB slots), so mixed k costs no padding traffic; rows that are not 16-byte tileable or
+// are longer than a slot fall back inside the kernel.
 template <typename T, int MODE>
 int launch_ragged(const void* in, void* out, int64_t batch, int64_t D, const int32_t* k_per_row,
                   const int64_t* out_offsets, cudaStream_t s) {
-  constexpr bool heavy = MODE == kModeRenorm && sizeof(T) == 8;
   const int64_t in_pitch = D * (int64_t)sizeof(T);
-  if (aligned_to(in, 32) && aligned_to(out, 32) && in_pitch % 32 == 0)
-    return launch_reg<T, 32, 8, 1, 32, MODE, heavy ? 2 : 3, true>(in, out, batch, in_pitch, 0, D, k_per_row, out_offsets, 0, s);
+  if (aligned_to(in, 16) && aligned_to(out, 16) && in_pitch % 16 == 0)
+    return launch_bulk<T, 16, 2, MODE, true>(in, out, batch, in_pitch, 0, 8, D, k_per_row, out_offsets, s);
   return launch_general<T, MODE>(in, out, batch, D, 0, k_per_row, out_offsets, s);
 }
 

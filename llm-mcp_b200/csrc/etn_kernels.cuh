@@ -36,6 +36,14 @@ constexpr int kWarpsPerBlock = 8;
 constexpr int kThreads = kWarpsPerBlock * 32;
 constexpr unsigned kFull = 0xffffffffu;
 
+// Programmatic dependent launch (see launch_kernel in etn_api.cu): let the next kernel of the
+// stream be scheduled now, then wait until the previous one has completed and flushed.
+// Both are no-ops for a kernel launched the ordinary way.
+__device__ __forceinline__ void pdl_prologue() {
+  asm volatile("griddepcontrol.launch_dependents;");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 // -------------------------------------------------------------- reductions ----
 // Butterflies over groups of L consecutive lanes (L = 32: the whole warp).  Every lane of a
 // group ends up with the same value.  All 32 lanes must take part.
@@ -171,11 +179,14 @@ __device__ __forceinline__ void double_to_words(uint32_t* w, double v) {
 
 // ------------------------------------------- per-lane pieces of a row in registers ----
 // Sum of squares of the NW words a lane holds, float32 elements: plain float64 FMA chains.
+// `used` (here and below): how many of the lane's NW words can be non-zero, a warp-uniform
+// bound that lets a short ragged row skip the arithmetic on its zero padding.
 template <int NW>
-__device__ __forceinline__ double lane_sumsq32(const uint32_t (&w)[NW]) {
+__device__ __forceinline__ double lane_sumsq32(const uint32_t (&w)[NW], int used = NW) {
   double a0 = 0.0, a1 = 0.0;
 #pragma unroll
   for (int i = 0; i < NW; i += 2) {
+    if (i >= used) break;
     const double x0 = (double)__uint_as_float(w[i]);
     const double x1 = (double)__uint_as_float(w[i + 1]);
     a0 = fma(x0, x0, a0); a1 = fma(x1, x1, a1);
@@ -186,11 +197,12 @@ __device__ __forceinline__ double lane_sumsq32(const uint32_t (&w)[NW]) {
 // float64 elements: blocks of <= 4 squares by FMA, block sums added error-free.
 // `pre` != 0 rescales by 2^pre first (slow path).
 template <int NW>
-__device__ __forceinline__ void lane_sumsq64(const uint32_t (&w)[NW], int pre, Acc2& acc) {
+__device__ __forceinline__ void lane_sumsq64(const uint32_t (&w)[NW], int pre, Acc2& acc, int used = NW) {
   constexpr int ND = NW / 2;
   acc.clear();
 #pragma unroll
   for (int b = 0; b < ND; b += 4) {
+    if (2 * b >= used) break;
     double q = 0.0;
 #pragma unroll
     for (int i = b; i < b + 4 && i < ND; ++i) {
@@ -203,40 +215,40 @@ __device__ __forceinline__ void lane_sumsq64(const uint32_t (&w)[NW], int pre, A
 }
 
 template <int NW>
-__device__ __forceinline__ double lane_maxabs64(const uint32_t (&w)[NW]) {
+__device__ __forceinline__ double lane_maxabs64(const uint32_t (&w)[NW], int used = NW) {
   double m = 0.0;
 #pragma unroll
-  for (int i = 0; i < NW / 2; ++i) m = fmax(m, fabs(words_to_double(&w[2 * i])));
+  for (int i = 0; i < NW / 2; ++i) if (2 * i < used) m = fmax(m, fabs(words_to_double(&w[2 * i])));
   return m;
 }
 
 template <int NW>
-__device__ __forceinline__ void lane_apply32(uint32_t (&w)[NW], const Scale32& sc) {
+__device__ __forceinline__ void lane_apply32(uint32_t (&w)[NW], const Scale32& sc, int used = NW) {
   if (sc.kind == kFast) {                            // warp-uniform
     const float f = sc.inv_f;
 #pragma unroll
-    for (int i = 0; i < NW; ++i) w[i] = __float_as_uint(__uint_as_float(w[i]) * f);
+    for (int i = 0; i < NW; ++i) if (i < used) w[i] = __float_as_uint(__uint_as_float(w[i]) * f);
   } else if (sc.kind == kSlow) {
     const double d = sc.inv_d;
 #pragma unroll
-    for (int i = 0; i < NW; ++i) w[i] = __float_as_uint((float)((double)__uint_as_float(w[i]) * d));
+    for (int i = 0; i < NW; ++i) if (i < used) w[i] = __float_as_uint((float)((double)__uint_as_float(w[i]) * d));
   }
 }
 
 template <int NW>
-__device__ __forceinline__ void lane_apply64(uint32_t (&w)[NW], const Scale64& sc) {
+__device__ __forceinline__ void lane_apply64(uint32_t (&w)[NW], const Scale64& sc, int used = NW) {
   if (sc.kind == kCopy) return;
 #pragma unroll
-  for (int i = 0; i < NW / 2; ++i) double_to_words(&w[2 * i], sc.apply(words_to_double(&w[2 * i])));
+  for (int i = 0; i < NW / 2; ++i) if (2 * i < used) double_to_words(&w[2 * i], sc.apply(words_to_double(&w[2 * i])));
 }
 
 // Scale of a float64 row held in registers by a group of L lanes.  Control flow is uniform
 // across the warp (the shuffles need all 32 lanes) even when the warp's 32/L rows disagree
 // on whether they need the rescaled slow path.
 template <int NW, int L>
-__device__ __forceinline__ Scale64 row_scale64(const uint32_t (&w)[NW]) {
+__device__ __forceinline__ Scale64 row_scale64(const uint32_t (&w)[NW], int used = NW) {
   Acc2 acc;
-  lane_sumsq64<NW>(w, 0, acc);
+  lane_sumsq64<NW>(w, 0, acc, used);
   acc.warp_reduce<L>();
   Scale64 sc; sc.pre = 0; sc.kind = kFast; sc.r = 0.0; sc.r_lo = 0.0;
   double hi, lo;
@@ -244,11 +256,11 @@ __device__ __forceinline__ Scale64 row_scale64(const uint32_t (&w)[NW]) {
   const bool ok = ss_in_range(hi);
   if (__all_sync(kFull, ok)) { sc.from_ss(hi, lo); return sc; }
   // some row here is all zeros or has squares out of range: rescale by its largest magnitude
-  const double m = warp_max<L>(lane_maxabs64<NW>(w));
+  const double m = warp_max<L>(lane_maxabs64<NW>(w, used));
   const bool copy = !ok && (!(m > 0.0) || !(m <= DBL_MAX));   // all zeros (or non-finite in)
   const int pre = (ok || copy) ? 0 : -ilogb(m);
   Acc2 a2;
-  lane_sumsq64<NW>(w, pre, a2);
+  lane_sumsq64<NW>(w, pre, a2, used);
   a2.warp_reduce<L>();
   if (ok) {
     sc.from_ss(hi, lo);
@@ -337,6 +349,7 @@ rows_reg_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t bat
                 int64_t in_pitch /*bytes*/, int nvec_dense, int64_t D,
                 const int32_t* __restrict__ k_per_row, const int64_t* __restrict__ out_offsets) {
   static_assert(!RAGGED || (L == 32 && R == 1), "ragged rows are one per warp");
+  pdl_prologue();
   constexpr int W = VB / 4, NW = NV * W;
   constexpr int S = 32 / L;                            // rows side by side in a warp
   const int lane = threadIdx.x & 31;
@@ -434,6 +447,7 @@ rows_coop_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t ba
   constexpr int W = VB / 4, NW = NV * W;
   constexpr int RPB = kWarpsPerBlock / G;            // rows per block iteration
   __shared__ double part[2][kWarpsPerBlock][3];      // double-buffered: (s, c, max)
+  pdl_prologue();
   const int lane = threadIdx.x & 31;
   const int wib = threadIdx.x >> 5;                  // warp in block
   const int grp = wib / G, g = wib % G;
@@ -511,6 +525,161 @@ rows_coop_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t ba
   }
 }
 
+// ------------------------------------------------------ bulk-async row kernel ----
+// For rows whose arithmetic is long enough to expose memory latency (float64 renorm): the
+// row prefix travels global -> shared memory as ONE bulk asynchronous copy (cp.async.bulk,
+// the TMA engine, SASS UBLKCP) that completes on an mbarrier, so the bytes in flight are set
+// by the shared-memory ring (NCW warps x S slots x row bytes, up to ~200 KiB per SM), not by
+// how long a warp's registers are tied up in the reduction.  Every warp runs its own ring:
+// lane 0 issues the copy for the row S steps ahead right after the warp has pulled the
+// current row into registers, so no producer warp and no "empty" barriers are needed.
+// Results go straight from registers to global memory (128-bit stores).  Persistent: one
+// block per SM, rows dealt round-robin to warps.  Rows must be 16-byte tileable and fit a slot.
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile("{\n\t.reg .pred p;\n\t"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                 "selp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+  } while (!done);
+}
+// One row prefix: global -> shared, completion (byte count) signalled on `bar`.
+__device__ __forceinline__ void bulk_load_row(uint32_t dst, const void* src, uint32_t bytes,
+                                              uint32_t bar, uint64_t policy) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+               " [%0], [%1], %2, [%3], %4;"
+               :: "r"(dst), "l"(src), "r"(bytes), "r"(bar), "l"(policy) : "memory");
+}
+
+// RAGGED: row r keeps k_per_row[r] elements at element offset out_offsets[r]; a row that is
+// not 16-byte tileable or does not fit a slot is not staged and takes general_row instead.
+template <typename T, int NV16, int S, int NCW, int MODE, bool RAGGED>
+__global__ void __launch_bounds__(NCW * 32, (NV16 > 12 ? ((sizeof(T) == 4 && MODE == kModeRenorm) ? 2 : 3) : 4))
+rows_bulk_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t batch,
+                 int64_t in_pitch /*bytes*/, int nvec16_dense, int rows_per_warp, int64_t D,
+                 const int32_t* __restrict__ k_per_row, const int64_t* __restrict__ out_offsets) {
+  constexpr int NW = NV16 * 4;
+  constexpr int SLOT = NV16 * 32 * 16;                 // bytes per ring slot
+  extern __shared__ __align__(128) unsigned char ring[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(ring + (size_t)NCW * S * SLOT);
+  const int lane = threadIdx.x & 31;
+  const int wib = threadIdx.x >> 5;
+  unsigned char* my_slots = ring + (size_t)wib * S * SLOT;
+  const uint32_t bar0 = smem_u32(&bars[wib * S]);
+
+  if (lane == 0) {
+#pragma unroll
+    for (int s = 0; s < S; ++s) mbar_init(bar0 + 8u * s, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  __syncthreads();
+  pdl_prologue();
+
+  // Bytes of row `row` to stage (0: the row goes through general_row) and where it lands.
+  auto row_plan = [&](int64_t row, char*& dst) -> uint32_t {
+    if constexpr (!RAGGED) {
+      dst = out + row * ((int64_t)nvec16_dense * 16);
+      return (uint32_t)nvec16_dense * 16u;
+    } else {
+      int64_t kr = k_per_row[row];
+      if (kr > D) kr = D;
+      const int64_t kb = kr * (int64_t)sizeof(T);
+      dst = out + out_offsets[row] * (int64_t)sizeof(T);
+      const bool tile = kb > 0 && (kb % 16 == 0) && kb <= (int64_t)SLOT &&
+                        (reinterpret_cast<uintptr_t>(dst) % 16) == 0;
+      return tile ? (uint32_t)kb : 0u;
+    }
+  };
+
+  uint64_t policy;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
+  // rows_per_warp == 0: persistent, rows dealt round-robin over all warps of the grid;
+  // otherwise every warp owns rows_per_warp consecutive rows and the grid covers the batch
+  // (the hardware block scheduler then balances the SMs, which measures 5-10 % faster).
+  const int64_t gwarp = (int64_t)blockIdx.x * NCW + wib;
+  const int64_t tw = rows_per_warp > 0 ? 1 : (int64_t)gridDim.x * NCW;
+  const int64_t gw = rows_per_warp > 0 ? gwarp * rows_per_warp : gwarp;
+  if (rows_per_warp > 0 && gw + rows_per_warp < batch) batch = gw + rows_per_warp;
+  if (lane == 0) {
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+      const int64_t row = gw + s * tw;
+      if (row < batch) {
+        char* d;
+        const uint32_t nb = row_plan(row, d);
+        if (nb) bulk_load_row(smem_u32(my_slots + s * SLOT), in + row * in_pitch, nb, bar0 + 8u * s, policy);
+      }
+    }
+  }
+  int s = 0;
+  uint32_t parity = 0;                                  // per-slot phase, kept as a bit mask
+  for (int64_t row = gw; row < batch; row += tw) {
+    char* dst;
+    const uint32_t row_bytes = row_plan(row, dst);
+    const unsigned char* slot = my_slots + s * SLOT;
+    const int64_t next = row + (int64_t)S * tw;
+    if constexpr (RAGGED) {
+      if (row_bytes == 0) {                             // warp-uniform: odd row, nothing was staged
+        if (lane == 0 && next < batch) {
+          char* d;
+          const uint32_t nb = row_plan(next, d);
+          if (nb) bulk_load_row(smem_u32(slot), in + next * in_pitch, nb, bar0 + 8u * s, policy);
+        }
+        int64_t kr = k_per_row[row];
+        if (kr > D) kr = D;
+        general_row<T, MODE>((const T*)(in + row * in_pitch), (T*)dst, kr, lane);
+        if (++s == S) s = 0;
+        continue;
+      }
+    }
+    mbar_wait(bar0 + 8u * s, (parity >> s) & 1u);
+    parity ^= 1u << s;
+    const int nvec16 = (int)(row_bytes >> 4);
+    uint32_t w[NW];
+#pragma unroll
+    for (int j = 0; j < NV16; ++j) {
+      const int idx = j * 32 + lane;
+      if (idx < nvec16) {
+        const uint4 v = *reinterpret_cast<const uint4*>(slot + idx * 16);
+        w[j * 4] = v.x; w[j * 4 + 1] = v.y; w[j * 4 + 2] = v.z; w[j * 4 + 3] = v.w;
+      } else {
+        w[j * 4] = 0u; w[j * 4 + 1] = 0u; w[j * 4 + 2] = 0u; w[j * 4 + 3] = 0u;
+      }
+    }
+    __syncwarp();                                       // every lane has its copy: slot is free
+    if (lane == 0 && next < batch) {
+      char* d;
+      const uint32_t nb = row_plan(next, d);
+      if (nb) bulk_load_row(smem_u32(slot), in + next * in_pitch, nb, bar0 + 8u * s, policy);
+    }
+    if constexpr (MODE == kModeRenorm) {
+      const int used = RAGGED ? 4 * ((nvec16 + 31) >> 5) : NW;   // words per lane that can be non-zero
+      if constexpr (sizeof(T) == 4) {
+        Scale32 sc; sc.from_ss(warp_sum(lane_sumsq32<NW>(w, used)));
+        lane_apply32<NW>(w, sc, used);
+      } else {
+        const Scale64 sc = row_scale64<NW, 32>(w, used);
+        lane_apply64<NW>(w, sc, used);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < NV16; ++j) {
+      const int idx = j * 32 + lane;
+      if (idx < nvec16) st_vec<16, 0>(dst + (int64_t)idx * 16, &w[j * 4]);
+    }
+    if (++s == S) s = 0;
+  }
+}
+
 // ------------------------------------------------------------ general kernel ----
 // Any k, any D, any element-aligned pointers.  k_per_row == nullptr -> every row keeps k;
 // out_offsets == nullptr -> dense output.
@@ -519,6 +688,7 @@ __global__ void __launch_bounds__(kThreads)
 rows_general_kernel(const T* __restrict__ in, T* __restrict__ out, int64_t batch, int64_t D,
                     int64_t k, const int32_t* __restrict__ k_per_row,
                     const int64_t* __restrict__ out_offsets) {
+  pdl_prologue();
   const int lane = threadIdx.x & 31;
   const int64_t warp = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * kThreads) >> 5;

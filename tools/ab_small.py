@@ -1,0 +1,39 @@
+"""Times the request-sized shapes (C1, C2) and C3-f64 through the C-ABI; run with ETN_PDL=0/1."""
+import json, os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import bench
+from llm_mcp_b200 import embedgpu as eg
+torch.cuda.set_device(0)
+peak, _ = bench.measured_peak()
+for name in sys.argv[1:] or ["c1", "c2", "c4", "c3f64"]:
+    r = bench.quick_measure(torch, eg, bench.WORKLOADS[name], peak, steps=200, warmup=20)
+    print(os.environ.get("ETN_PDL", "default"), name, "%.2f us  %.0f GB/s  %.3g vec/s" % (r["us_per_launch"], r["achieved_GBps"], r["vectors_per_s"]), flush=True)
+    torch.cuda.empty_cache()
+
+# C5: ragged mixed-request batch, float64, D = 4096, per-request k in {64,...,1024}
+import numpy as np
+rng = np.random.default_rng(5)
+rows, D = 1048576, 4096
+parts, n = [], 0
+while n < rows:
+    m = min(int(rng.integers(1, 2049)), rows - n)
+    parts.append(np.full(m, rng.choice([64, 128, 256, 512, 1024]), dtype=np.int32)); n += m
+kpr = np.concatenate(parts)
+off = np.zeros(rows + 1, dtype=np.int64); np.cumsum(kpr, out=off[1:])
+L = eg.lib(); st = torch.cuda.current_stream().cuda_stream
+x = torch.empty((rows, D), dtype=torch.float64, device="cuda")
+eg.check(L.etn_fill_synthetic(5, 0, rows, D, D, D, eg.F64, x.data_ptr(), st), "fill")
+dk, do = torch.from_numpy(kpr).cuda(), torch.from_numpy(off[:-1].copy()).cuda()
+out = torch.empty(int(off[-1]), dtype=torch.float64, device="cuda")
+for mode in (1, 0):
+    for _ in range(5):
+        eg.check(L.embed_truncate_norm_ragged(rows, D, dk.data_ptr(), do.data_ptr(), eg.F64, mode, x.data_ptr(), out.data_ptr(), st), "ragged")
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(50):
+        eg.check(L.embed_truncate_norm_ragged(rows, D, dk.data_ptr(), do.data_ptr(), eg.F64, mode, x.data_ptr(), out.data_ptr(), st), "ragged")
+    e1.record(); torch.cuda.synchronize()
+    t = e0.elapsed_time(e1) * 1e-3 / 50
+    print("c5 ragged f64 mode=%d mean k=%.1f: %.3f ms  %.0f GB/s  %.3g vec/s" % (mode, kpr.mean(), t * 1e3, 2 * 8 * int(off[-1]) / t / 1e9, rows / t), flush=True)

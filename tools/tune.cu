@@ -41,6 +41,7 @@ struct Timer {
 struct Shape { const char* name; int64_t rows, D, k; int es; };
 
 static int g_sms = 148;
+static int g_iters = 20;
 static const char* g_filter = nullptr;
 static bool want(const std::string& n) { return !g_filter || n.find(g_filter) != std::string::npos; }
 
@@ -57,7 +58,7 @@ void run_reg(const Shape& s, const void* in, void* out, Timer& tm, int waves = 1
   const int64_t need = (s.rows + rpb - 1) / rpb;
   const int grid = waves > 0 ? (int)std::min<int64_t>(need, (int64_t)g_sms * per_sm * waves) : (int)need;
   const int nvec = (int)(s.k * s.es / VB);
-  double ms = tm.ms([&](int) { kern<<<grid, kThreads>>>((const char*)in, (char*)out, s.rows, s.D * s.es, nvec, s.D, nullptr, nullptr); }, 3, 20);
+  double ms = tm.ms([&](int) { kern<<<grid, kThreads>>>((const char*)in, (char*)out, s.rows, s.D * s.es, nvec, s.D, nullptr, nullptr); }, 3, g_iters);
   CK(cudaGetLastError());
   double gbs = (double)s.rows * 2 * s.k * s.es / ms / 1e6;
   printf("%-78s %8.3f ms %8.1f GB/s  regs=%d occ=%d grid=%d\n", name, ms, gbs, fa.numRegs, per_sm, grid);
@@ -75,10 +76,36 @@ void run_coop(const Shape& s, const void* in, void* out, Timer& tm, int waves = 
   const int64_t need = (s.rows + kWarpsPerBlock / G - 1) / (kWarpsPerBlock / G);
   const int grid = waves > 0 ? (int)std::min<int64_t>(need, (int64_t)g_sms * per_sm * waves) : (int)need;
   const int nvec = (int)(s.k * s.es / VB);
-  double ms = tm.ms([&](int) { kern<<<grid, kThreads>>>((const char*)in, (char*)out, s.rows, s.D * s.es, nvec); }, 3, 20);
+  double ms = tm.ms([&](int) { kern<<<grid, kThreads>>>((const char*)in, (char*)out, s.rows, s.D * s.es, nvec); }, 3, g_iters);
   CK(cudaGetLastError());
   double gbs = (double)s.rows * 2 * s.k * s.es / ms / 1e6;
   printf("%-78s %8.3f ms %8.1f GB/s  regs=%d occ=%d grid=%d\n", name, ms, gbs, fa.numRegs, per_sm, grid);
+}
+
+template <typename T, int NV16, int S, int NCW, int MODE>
+void run_bulk(const Shape& s, const void* in, void* out, Timer& tm, const void* ref_out = nullptr, int rpw = 0) {
+  char name[128];
+  snprintf(name, sizeof name, "%s bulk<NV16=%d,S=%d,NCW=%d,mode=%d,rpw=%d>", s.name, NV16, S, NCW, MODE, rpw);
+  if (!want(name)) return;
+  auto kern = rows_bulk_kernel<T, NV16, S, NCW, MODE, false>;
+  const size_t smem = (size_t)NCW * S * NV16 * 512 + (size_t)NCW * S * 8;
+  CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  cudaFuncAttributes fa; CK(cudaFuncGetAttributes(&fa, kern));
+  const int nvec16 = (int)(s.k * s.es / 16);
+  const size_t out_bytes = (size_t)s.rows * s.k * s.es;
+  const int grid = rpw > 0 ? (int)((s.rows + (int64_t)NCW * rpw - 1) / ((int64_t)NCW * rpw)) : g_sms;
+  CK(cudaMemset(out, 0, out_bytes));
+  double ms = tm.ms([&](int) { kern<<<grid, NCW * 32, smem>>>((const char*)in, (char*)out, s.rows, s.D * s.es, nvec16, rpw, s.D, nullptr, nullptr); }, 3, g_iters);
+  CK(cudaGetLastError());
+  double gbs = (double)s.rows * 2 * s.k * s.es / ms / 1e6;
+  int same = -1;
+  if (ref_out) {
+    std::vector<char> a(out_bytes), b(out_bytes);
+    CK(cudaMemcpy(a.data(), out, out_bytes, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(b.data(), ref_out, out_bytes, cudaMemcpyDeviceToHost));
+    same = memcmp(a.data(), b.data(), out_bytes) == 0;
+  }
+  printf("%-78s %8.3f ms %8.1f GB/s  regs=%d smem=%zuK same_as_reg=%d\n", name, ms, gbs, fa.numRegs, smem >> 10, same);
 }
 
 // PCIe study for the host path: DMA ceilings, prefix-only 2-D DMA, and the kernels reading and
@@ -147,6 +174,7 @@ static void pcie_study(Timer& tm) {
 
 int main(int argc, char** argv) {
   if (argc > 1) g_filter = argv[1];
+  if (getenv("ITERS")) g_iters = atoi(getenv("ITERS"));
   cudaDeviceProp p; CK(cudaGetDeviceProperties(&p, 0));
   g_sms = p.multiProcessorCount;
   printf("device %s, %d SMs, L2 %d MiB\n", p.name, g_sms, p.l2CacheSize >> 20);
@@ -169,11 +197,13 @@ int main(int argc, char** argv) {
   }
 
   std::vector<Shape> shapes = {
-      {"K64f64 2Mx4096->64", 2097152, 4096, 64, 8},
-      {"K32f64 2Mx4096->32", 2097152, 4096, 32, 8},
-      {"K128f32 2Mx768->128", 2097152, 768, 128, 4},
-      {"K64f32 4Mx768->64", 4194304, 768, 64, 4},
+      {"C3f32 1Mx4096->1024", 1048576, 4096, 1024, 4},
       {"C4f32 2Mx3072->256", 2097152, 3072, 256, 4},
+      {"C3f64 1Mx4096->1024", 1048576, 4096, 1024, 8},
+      {"K768f64 512Kx3072->768", 524288, 3072, 768, 8},
+      {"K512f64 1Mx4096->512", 1048576, 4096, 512, 8},
+      {"K256f64 1Mx4096->256", 1048576, 4096, 256, 8},
+      {"K128f64 2Mx4096->128", 2097152, 4096, 128, 8},
   };
   for (const Shape& s : shapes) {
     void *in, *out;
@@ -183,31 +213,38 @@ int main(int argc, char** argv) {
     else fill_kernel<double><<<g_sms * 16, 256>>>((double*)in, 3, 0, s.rows, s.D, s.D, s.D);
     CK(cudaDeviceSynchronize());
     const int64_t kb = s.k * s.es;
-    if (s.es == 8 && kb == 512) {
-      run_reg<double, 32, 1, 2, 1, 4, 1, 32>(s, in, out, tm, 0);
-      run_reg<double, 32, 1, 2, 1, 4, 1, 16>(s, in, out, tm, 0);
-      run_reg<double, 32, 1, 4, 1, 4, 1, 16>(s, in, out, tm, 0);
-      run_reg<double, 32, 1, 4, 1, 3, 1, 16>(s, in, out, tm, 0);
-      run_reg<float, 32, 1, 4, 0, 4, 1, 16>(s, in, out, tm, 0);
-    } else if (s.es == 8 && kb == 256) {
-      run_reg<double, 32, 1, 2, 1, 4, 1, 16>(s, in, out, tm, 0);
-      run_reg<double, 32, 1, 2, 1, 4, 1, 8>(s, in, out, tm, 0);
-      run_reg<double, 32, 1, 4, 1, 4, 1, 8>(s, in, out, tm, 0);
-      run_reg<float, 32, 1, 4, 0, 4, 1, 8>(s, in, out, tm, 0);
-    } else if (s.es == 4 && kb == 512) {
-      run_reg<float, 32, 1, 4, 1, 4, 1, 32>(s, in, out, tm, 0);
-      run_reg<float, 32, 1, 4, 1, 4, 1, 16>(s, in, out, tm, 0);
-      run_reg<float, 32, 1, 8, 1, 2, 1, 16>(s, in, out, tm, 0);
-      run_reg<float, 32, 1, 4, 0, 4, 1, 16>(s, in, out, tm, 0);
-    } else if (s.es == 4 && kb == 256) {
-      run_reg<float, 32, 1, 4, 1, 4, 1, 16>(s, in, out, tm, 0);
-      run_reg<float, 32, 1, 4, 1, 4, 1, 8>(s, in, out, tm, 0);
-      run_reg<float, 32, 1, 4, 0, 4, 1, 8>(s, in, out, tm, 0);
+    void* out2; CK(cudaMalloc(&out2, (size_t)s.rows * s.k * s.es));
+    // register kernel vs bulk-async ring kernel (persistent and one-shot), sustained (ITERS=100)
+    if (s.es == 4 && kb == 4096) {
+      run_reg<float, 32, 4, 1, 1, 4, 1>(s, in, out, tm, 1);
+      run_reg<float, 32, 4, 1, 1, 4, 1>(s, in, out, tm, 0);
+      run_bulk<float, 8, 2, 8, 1>(s, in, out2, tm, out, 0);
+      run_bulk<float, 8, 2, 8, 1>(s, in, out2, tm, out, 8);
     } else if (s.es == 4 && kb == 1024) {
-      run_reg<float, 32, 1, 4, 1, 4, 1, 32>(s, in, out, tm, 0);
-      run_reg<float, 32, 2, 4, 1, 4, 1, 16>(s, in, out, tm, 0);
-      run_reg<float, 32, 2, 2, 1, 4, 1, 16>(s, in, out, tm, 0);
+      run_reg<float, 32, 1, 4, 1, 4, 1>(s, in, out, tm, 0);
+      run_bulk<float, 2, 4, 4, 1>(s, in, out2, tm, out, 16);
+    } else if (s.es == 8 && kb == 8192) {
+      run_reg<double, 32, 8, 1, 1, 2, 1>(s, in, out, tm, 0);
+      run_coop<double, 32, 4, 2, 1, 3, 1>(s, in, out2, tm, 0);
+      run_bulk<double, 16, 2, 8, 1>(s, in, out2, tm, out, 0);
+      run_bulk<double, 16, 3, 8, 1>(s, in, out2, tm, out, 0);
+      run_bulk<double, 16, 2, 4, 1>(s, in, out2, tm, out, 4);
+      run_bulk<double, 16, 2, 4, 1>(s, in, out2, tm, out, 8);
+      run_bulk<double, 16, 2, 4, 0>(s, in, out2, tm, nullptr, 4);
+    } else if (s.es == 8 && kb == 6144) {
+      run_reg<double, 32, 8, 1, 1, 2, 1>(s, in, out, tm, 0);
+      run_bulk<double, 12, 2, 4, 1>(s, in, out2, tm, out, 4);
+    } else if (s.es == 8 && kb == 4096) {
+      run_reg<double, 32, 4, 1, 1, 3, 1>(s, in, out, tm, 0);
+      run_bulk<double, 8, 2, 4, 1>(s, in, out2, tm, out, 4);
+    } else if (s.es == 8 && kb == 2048) {
+      run_reg<double, 32, 2, 1, 1, 4, 1>(s, in, out, tm, 0);
+      run_bulk<double, 4, 2, 4, 1>(s, in, out2, tm, out, 8);
+    } else if (s.es == 8 && kb == 1024) {
+      run_reg<double, 32, 1, 4, 1, 4, 1>(s, in, out, tm, 0);
+      run_bulk<double, 2, 4, 4, 1>(s, in, out2, tm, out, 8);
     }
+    CK(cudaFree(out2));
     CK(cudaFree(in)); CK(cudaFree(out));
   }
   return 0;
