@@ -219,16 +219,48 @@ int launch_dense(const void* in, void* out, int64_t batch, int64_t D, int64_t kk
   return launch_general<T, MODE>(in, out, batch, D, kk, nullptr, nullptr, s);
 }
 
-// Ragged rows: every row prefix is one bulk-async copy of its own length into a warp's ring
-// (8 KiB slots), so mixed k costs no padding traffic; rows that are not 16-byte tileable or
-// are longer than a slot fall back inside the kernel.
+// Ragged rows: every row prefix is one bulk-async copy of its own length into a warp's
+// page-granular ring (rows_ring_kernel), so mixed k costs no padding traffic and short rows
+// still keep the ring full; rows that are not 16-byte tileable or exceed 8 KiB fall back
+// inside the kernel.
 template <typename T, int MODE>
 int launch_ragged(const void* in, void* out, int64_t batch, int64_t D, const int32_t* k_per_row,
                   const int64_t* out_offsets, cudaStream_t s) {
   const int64_t in_pitch = D * (int64_t)sizeof(T);
-  if (aligned_to(in, 16) && aligned_to(out, 16) && in_pitch % 16 == 0)
-    return launch_bulk<T, 16, 2, MODE, true>(in, out, batch, in_pitch, 0, 8, D, k_per_row, out_offsets, s);
-  return launch_general<T, MODE>(in, out, batch, D, 0, k_per_row, out_offsets, s);
+  if (!(aligned_to(in, 16) && aligned_to(out, 16) && in_pitch % 16 == 0))
+    return launch_general<T, MODE>(in, out, batch, D, 0, k_per_row, out_offsets, s);
+  constexpr int NCW = 4;
+  constexpr size_t smem = (size_t)NCW * 8192 + (size_t)NCW * 8 * 8 + (size_t)NCW * 8 * 3 * 4;
+  auto kern = rows_ring_kernel<T, NCW, MODE>;
+  {
+    static std::atomic<uint64_t> done{0};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    const uint64_t bit = 1ull << (dev & 63);
+    if (!(done.load(std::memory_order_acquire) & bit)) {
+      e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return (int)e;
+      done.fetch_or(bit, std::memory_order_release);
+    }
+  }
+  int dev = 0, sms = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess) sm_count(dev, &sms);
+  const int rpw = (int)std::max<int64_t>(1, std::min<int64_t>(16, batch / ((int64_t)NCW * sms * 2)));
+  const int64_t rows_per_block = (int64_t)NCW * rpw;
+  const int64_t blocks = std::min<int64_t>((batch + rows_per_block - 1) / rows_per_block, (int64_t)1 << 30);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)std::max<int64_t>(blocks, 1));
+  cfg.blockDim = dim3(NCW * 32);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return (int)cudaLaunchKernelEx(&cfg, kern, (const char*)in, (char*)out, batch, in_pitch, rpw, D, k_per_row,
+                                 out_offsets);
 }
 
 int check_dense(int64_t batch, int64_t D, int64_t k, int dtype, const void* in, const void* out) {

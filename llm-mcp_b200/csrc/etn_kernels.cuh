@@ -541,9 +541,12 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count) : "memory");
 }
+// Bounded: a copy that never lands is a bug, and a trap (an error code for the caller) beats
+// a hung device.  try_wait suspends in hardware between polls, so 2^24 polls is seconds.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  uint32_t done;
+  uint32_t done, polls = 0;
   do {
+    if (++polls == (1u << 24)) asm volatile("trap;");
     asm volatile("{\n\t.reg .pred p;\n\t"
                  "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
                  "selp.u32 %0, 1, 0, p;\n\t}"
@@ -677,6 +680,181 @@ rows_bulk_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t ba
       if (idx < nvec16) st_vec<16, 0>(dst + (int64_t)idx * 16, &w[j * 4]);
     }
     if (++s == S) s = 0;
+  }
+}
+
+// ------------------------------------------------- ragged byte-ring kernel ----
+// Ragged batches mix 512 B and 8 KiB prefixes.  Every warp owns an 8 KiB ring in shared
+// memory handed out in 512-byte pages: up to R = 8 rows are in flight, each one bulk-async
+// copy (cp.async.bulk + mbarrier) of exactly its own length, placed contiguously (a row that
+// would straddle the end of the ring starts over at page 0 and the skipped pages are
+// returned with it).  Lane 0 keeps the allocator (rows retire in the order they were issued,
+// so a page count is all it needs) and publishes position and length of each row through
+// shared memory.  The row is reduced and scaled straight out of shared memory in two short
+// rolled passes, so the instruction count follows the row's real length and the kernel needs
+// few registers (a register-resident version sized for the longest row ran 777 instructions
+// per row at 12 warps per SM and was issue-bound at 3.1-3.7 TB/s).
+// A row that is not 16-byte tileable or is longer than the ring takes general_row.
+template <typename T, int NCW, int MODE>
+__global__ void __launch_bounds__(NCW * 32, 6)
+rows_ring_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t batch,
+                 int64_t in_pitch /*bytes*/, int rows_per_warp, int64_t D,
+                 const int32_t* __restrict__ k_per_row, const int64_t* __restrict__ out_offsets) {
+  constexpr int PAGE = 512, P = 16, R = 8;             // 8 KiB ring per warp
+  constexpr int RING = PAGE * P;
+  extern __shared__ __align__(128) unsigned char ring[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(ring + (size_t)NCW * RING);
+  int* meta = reinterpret_cast<int*>(bars + NCW * R);   // [NCW][R][3]: page, bytes, pages held
+  const int lane = threadIdx.x & 31;
+  const int wib = threadIdx.x >> 5;
+  unsigned char* my_ring = ring + (size_t)wib * RING;
+  const uint32_t bar0 = smem_u32(&bars[wib * R]);
+  int* my_meta = meta + wib * R * 3;
+
+  if (lane == 0) {
+#pragma unroll
+    for (int i = 0; i < R; ++i) mbar_init(bar0 + 8u * i, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  __syncthreads();
+  pdl_prologue();
+
+  auto row_plan = [&](int64_t row, char*& dst, int64_t& kr) -> uint32_t {
+    kr = k_per_row[row];
+    if (kr > D) kr = D;
+    const int64_t kb = kr * (int64_t)sizeof(T);
+    dst = out + out_offsets[row] * (int64_t)sizeof(T);
+    const bool tile = kb > 0 && (kb % 16 == 0) && kb <= (int64_t)RING &&
+                      (reinterpret_cast<uintptr_t>(dst) % 16) == 0;
+    return tile ? (uint32_t)kb : 0u;
+  };
+
+  uint64_t policy;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
+  const int64_t first = ((int64_t)blockIdx.x * NCW + wib) * rows_per_warp;
+  const int64_t end = first + rows_per_warp < batch ? first + rows_per_warp : batch;
+
+  // allocator state, meaningful in lane 0 only
+  int64_t head_row = first;
+  int head_page = 0, used = 0, inflight = 0;
+  auto issue_more = [&]() {
+    while (head_row < end && inflight < R) {
+      char* d; int64_t kr;
+      const uint32_t nb = row_plan(head_row, d, kr);
+      const int slot = (int)((head_row - first) % R);
+      if (nb == 0) {
+        my_meta[slot * 3 + 1] = 0; my_meta[slot * 3 + 2] = 0;
+      } else {
+        const int need = (int)((nb + PAGE - 1) / PAGE);
+        if (used == 0) head_page = 0;                   // empty ring: any row that fits at all fits at 0
+        int pos = head_page, waste = 0;
+        if (pos + need > P) { waste = P - pos; pos = 0; }
+        if (used + waste + need > P) break;
+        bulk_load_row(smem_u32(my_ring + pos * PAGE), in + head_row * in_pitch, nb, bar0 + 8u * slot, policy);
+        my_meta[slot * 3] = pos; my_meta[slot * 3 + 1] = (int)nb; my_meta[slot * 3 + 2] = waste + need;
+        used += waste + need;
+        head_page = pos + need == P ? 0 : pos + need;
+      }
+      ++head_row; ++inflight;
+    }
+  };
+  if (lane == 0) issue_more();
+
+  uint32_t parity = 0;
+  for (int64_t row = first; row < end; ++row) {
+    __syncwarp();                                       // lane 0's bookkeeping is visible
+    const int slot = (int)((row - first) % R);
+    const int pos = my_meta[slot * 3];
+    const uint32_t row_bytes = (uint32_t)my_meta[slot * 3 + 1];
+    const int held = my_meta[slot * 3 + 2];
+    char* dst; int64_t kr;
+    row_plan(row, dst, kr);
+    if (row_bytes == 0) {                               // warp-uniform: odd row, nothing staged
+      __syncwarp();
+      if (lane == 0) { --inflight; issue_more(); }
+      general_row<T, MODE>((const T*)(in + row * in_pitch), (T*)dst, kr, lane);
+      continue;
+    }
+    mbar_wait(bar0 + 8u * slot, (parity >> slot) & 1u);
+    parity ^= 1u << slot;
+    const int nvec16 = (int)(row_bytes >> 4);
+    const uint4* src = reinterpret_cast<const uint4*>(my_ring + pos * PAGE);
+    uint4* dst4 = reinterpret_cast<uint4*>(dst);
+
+    if constexpr (MODE == kModeTruncate) {
+      for (int i = lane; i < nvec16; i += 32) { const uint4 v = src[i]; st_vec<16, 0>(dst4 + i, &v.x); }
+    } else if constexpr (sizeof(T) == 4) {
+      double a = 0.0;
+      for (int i = lane; i < nvec16; i += 32) {
+        const uint4 v = src[i];
+        const double x0 = (double)__uint_as_float(v.x), x1 = (double)__uint_as_float(v.y);
+        const double x2 = (double)__uint_as_float(v.z), x3 = (double)__uint_as_float(v.w);
+        a = fma(x0, x0, a); a = fma(x1, x1, a); a = fma(x2, x2, a); a = fma(x3, x3, a);
+      }
+      Scale32 sc; sc.from_ss(warp_sum(a));
+      for (int i = lane; i < nvec16; i += 32) {
+        uint4 v = src[i];
+        if (sc.kind != kCopy) {
+          v.x = __float_as_uint(sc.apply(__uint_as_float(v.x))); v.y = __float_as_uint(sc.apply(__uint_as_float(v.y)));
+          v.z = __float_as_uint(sc.apply(__uint_as_float(v.z))); v.w = __float_as_uint(sc.apply(__uint_as_float(v.w)));
+        }
+        st_vec<16, 0>(dst4 + i, &v.x);
+      }
+    } else {
+      // blocks of <= 4 squares (two 16-byte vectors of this lane), block sums added error-free
+      auto sumsq = [&](int pre, Acc2& acc) {
+        acc.clear();
+        for (int i = lane; i < nvec16; i += 64) {
+          const uint4 v = src[i];
+          double x0 = words_to_double(&v.x), x1 = words_to_double(&v.z);
+          if (pre != 0) { x0 = scalbn(x0, pre); x1 = scalbn(x1, pre); }
+          double q = fma(x1, x1, x0 * x0);
+          if (i + 32 < nvec16) {
+            const uint4 u = src[i + 32];
+            double x2 = words_to_double(&u.x), x3 = words_to_double(&u.z);
+            if (pre != 0) { x2 = scalbn(x2, pre); x3 = scalbn(x3, pre); }
+            q = fma(x2, x2, q); q = fma(x3, x3, q);
+          }
+          acc.add(q);
+        }
+        acc.warp_reduce();
+      };
+      Acc2 acc;
+      sumsq(0, acc);
+      Scale64 sc; sc.pre = 0; sc.kind = kFast; sc.r = 0.0; sc.r_lo = 0.0;
+      double hi, lo;
+      acc.split(hi, lo);
+      if (ss_in_range(hi)) {                            // warp-uniform: one row per warp
+        sc.from_ss(hi, lo);
+      } else {
+        double m = 0.0;
+        for (int i = lane; i < nvec16; i += 32) {
+          const uint4 v = src[i];
+          m = fmax(m, fmax(fabs(words_to_double(&v.x)), fabs(words_to_double(&v.z))));
+        }
+        m = warp_max(m);
+        if (!(m > 0.0) || !(m <= DBL_MAX)) {
+          sc.kind = kCopy;
+        } else {
+          sc.kind = kSlow;
+          sc.pre = -ilogb(m);
+          sumsq(sc.pre, acc);
+          acc.split(hi, lo);
+          sc.from_ss(hi, lo);
+        }
+      }
+      for (int i = lane; i < nvec16; i += 32) {
+        uint4 v = src[i];
+        if (sc.kind != kCopy) {
+          double_to_words(&v.x, sc.apply(words_to_double(&v.x)));
+          double_to_words(&v.z, sc.apply(words_to_double(&v.z)));
+        }
+        st_vec<16, 0>(dst4 + i, &v.x);
+      }
+    }
+    __syncwarp();                                       // every lane is done with the pages
+    if (lane == 0) { used -= held; --inflight; issue_more(); }
   }
 }
 

@@ -193,6 +193,30 @@ def test_ragged_against_oracle(oracle):
                 assert_ulp(oracle, got, want, what="ragged")
 
 
+def test_ragged_ring_wraps_and_fallbacks(oracle):
+    """Row-length sequences that make the per-warp 8 KiB page ring wrap, skip pages, run empty
+    and hold a single ring-sized row; rows beyond the ring and rows that are not 16-byte
+    tileable take the in-kernel fallback."""
+    D = 4096
+    pats = [[256, 1024] * 40, [64, 1024, 64, 512, 1024, 128, 960, 1024, 2, 1024], [1024] * 33, [2] * 70,
+            [2048, 64, 4096, 62, 1024, 3, 1022, 1024], [512, 512, 1024, 256, 256, 256, 1024, 64]]
+    for dt in (np.float64, np.float32):
+        for pat in pats:
+            kpr = np.array((pat * 64)[:1500], dtype=np.int32)
+            if dt == np.float32:
+                kpr = np.minimum(kpr * 2, 4096)
+            rows = len(kpr)
+            xh = oracle.fill(31, rows, D, dt)
+            x = gu.dev_fill(31, rows, D, dt)
+            for mode in (eg.TRUNCATE, eg.TRUNCATE_RENORM):
+                want, off = oracle.ragged(xh, kpr, mode)
+                got = gu.run_ragged(x, kpr, off, mode).cpu().numpy()
+                if mode == eg.TRUNCATE:
+                    assert np.array_equal(gu.bits(got), gu.bits(want))
+                else:
+                    assert_ulp(oracle, got, want, what=f"ragged ring {pat[:4]}")
+
+
 def test_idempotent_and_unit_norm(oracle):
     x = gu.dev_fill(16, 8192, 768, np.float32)
     y = gu.run_dense(x, 256, eg.TRUNCATE_RENORM)

@@ -37,3 +37,23 @@ for mode in (1, 0):
     e1.record(); torch.cuda.synchronize()
     t = e0.elapsed_time(e1) * 1e-3 / 50
     print("c5 ragged f64 mode=%d mean k=%.1f: %.3f ms  %.0f GB/s  %.3g vec/s" % (mode, kpr.mean(), t * 1e3, 2 * 8 * int(off[-1]) / t / 1e9, rows / t), flush=True)
+
+# request-sized end-to-end latency through the host entry points (pinned buffers)
+import time
+eg.init([0])
+for rows_, D_, k_, dt_ in ((1024, 4096, 1024, np.float64), (64, 4096, 1024, np.float64), (2048, 3072, 256, np.float32)):
+    pin_in, pin_out = eg.PinnedBuffer(rows_ * D_ * np.dtype(dt_).itemsize), eg.PinnedBuffer(rows_ * k_ * np.dtype(dt_).itemsize)
+    hx, hy = pin_in.array((rows_, D_), dt_), pin_out.array((rows_, k_), dt_)
+    hx[:] = 0.01
+    for fn, label in ((lambda: eg.truncate_norm_host(hx, k_, 1, out=hy, n_devices=1), "host"),
+                      (lambda: L.embed_truncate_norm_host_static(rows_, D_, k_, eg.dtype_code(dt_), 1, hx.ctypes.data, 0, hy.ctypes.data, None), "host_static")):
+        for _ in range(5):
+            fn()
+        t0 = time.perf_counter()
+        for _ in range(50):
+            fn()
+        t = (time.perf_counter() - t0) / 50
+        print("e2e %-11s %5d x %d -> %d %s: %.1f us per call (%.1f GB/s each way)" % (label, rows_, D_, k_, np.dtype(dt_).name, t * 1e6, rows_ * k_ * np.dtype(dt_).itemsize / t / 1e9), flush=True)
+    del hx, hy
+    pin_in.free(); pin_out.free()
+eg.shutdown()
