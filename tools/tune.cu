@@ -11,6 +11,7 @@
 #include <string>
 #include <vector>
 #include <algorithm>
+#include <chrono>
 #include "../llm-mcp_b200/csrc/etn_kernels.cuh"
 
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { fprintf(stderr, "%s:%d %s\n", __FILE__, __LINE__, cudaGetErrorString(e_)); exit(1); } } while (0)
@@ -168,6 +169,33 @@ static void pcie_study(Timer& tm) {
       k64<<<128, kThreads>>>(din, dout, 1024, 8192, 256, 1024, nullptr, nullptr);
       CK(cudaMemcpyAsync(hout, dout, 8388608, cudaMemcpyDeviceToHost)); }, 2, 20);
     rep("C1 staged H2D(2-D) + kernel + D2H (8 MiB each way)", ms, 8.0 * 1048576);
+  }
+  // C1 through chunked pipelines: wall-clock per call, n chunks round-robin over 4 streams
+  {
+    auto k64 = rows_reg_kernel<double, 32, 8, 1, 32, 1, 2, 1, false>;
+    cudaStream_t st[4];
+    for (auto& x : st) CK(cudaStreamCreateWithFlags(&x, cudaStreamNonBlocking));
+    for (int nch : {1, 2, 4, 8}) {
+      for (int twod : {1, 0}) {
+        const int rows_c = 1024 / nch;
+        auto once = [&]() {
+          for (int c = 0; c < nch; ++c) {
+            cudaStream_t s = st[c % 4];
+            char* d = din + (size_t)c * rows_c * 8192;
+            if (twod) CK(cudaMemcpy2DAsync(d, 8192, hin + (size_t)c * rows_c * 32768, 32768, 8192, rows_c, cudaMemcpyHostToDevice, s));
+            else CK(cudaMemcpyAsync(d, hin + (size_t)c * rows_c * 8192, (size_t)rows_c * 8192, cudaMemcpyHostToDevice, s));
+            k64<<<(rows_c + 7) / 8, kThreads, 0, s>>>(d, d, rows_c, 8192, 256, 1024, nullptr, nullptr);
+            CK(cudaMemcpyAsync(hout + (size_t)c * rows_c * 8192, d, (size_t)rows_c * 8192, cudaMemcpyDeviceToHost, s));
+          }
+          for (auto& x : st) CK(cudaStreamSynchronize(x));
+        };
+        for (int i = 0; i < 5; ++i) once();
+        auto t0 = std::chrono::steady_clock::now();
+        for (int i = 0; i < 50; ++i) once();
+        double us = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count() / 50;
+        printf("C1 pipeline %d chunk(s), %s H2D: %.1f us per call\n", nch, twod ? "2-D" : "1-D", us);
+      }
+    }
   }
   CK(cudaFreeHost(hin)); CK(cudaFreeHost(hout)); CK(cudaFree(din)); CK(cudaFree(dout));
 }
