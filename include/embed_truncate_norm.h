@@ -65,6 +65,8 @@ extern "C" {
 #define ETN_ERR_ALIGN (-4)    /* pointer not aligned to the element size */
 #define ETN_ERR_NOT_INIT (-5) /* host path used before etn_init */
 #define ETN_ERR_DEVICE (-6)   /* bad device list / n_devices */
+#define ETN_ERR_JSON (-8)      /* malformed JSON, a non-finite value, or a number outside float64 */
+#define ETN_ERR_JSON_DUP (-9)  /* "data" or an item's "embedding" occurs twice: take the reference path */
 #define ETN_ERR_TOO_LARGE (-7) /* more than ETN_STATIC_STAGE_BYTES asked of the _static entry point */
 
 /* Library version (ETN_VERSION of the build).  No reference counterpart. */
@@ -160,6 +162,38 @@ ETN_API int embed_truncate_norm_host(int64_t batch, int64_t D, int64_t k, int dt
 ETN_API int embed_truncate_norm_host_static(int64_t batch, int64_t D, int64_t k, int dtype, int mode,
                                             const void *host_in, int64_t in_pitch_bytes,
                                             void *host_out, void *stream);
+
+/* ---- JSON packer: embedding arrays go from the provider's response
+ * text into pinned memory and back without the map[string]any round trip of
+ * json.NewDecoder(resp.Body).Decode(&result) (handlers.go:2047-2050) and
+ * json.NewEncoder(w).Encode(payload) (helpers.go:11-15). ---- */
+
+/* Rewrites an OpenAI-format embeddings response: every result["data"][i]["embedding"] that is
+ * an array longer than `dims` is cut to its first `dims` elements (handlers.go:2068-2076:
+ * non-object items, non-array embeddings and shorter vectors are left alone) and, with
+ * ETN_TRUNCATE_RENORM, L2-renormalised on the GPU (needs etn_init; vectors whose kept
+ * prefix holds anything but numbers are only cut, like the reference would).  In
+ * ETN_TRUNCATE mode no number is parsed: the kept tokens are copied as text.  All bytes
+ * outside those arrays pass through unchanged; formatted numbers follow encoding/json
+ * (shortest round trip, 'e' form below 1e-6 and from 1e21).  dims <= 0 copies the input
+ * (handlers.go:1891).  Returns the number of bytes written to `out`, or a negative code:
+ * ETN_ERR_SHAPE = out_cap too small (len + 2 always suffices for TRUNCATE; allow 26 bytes per
+ * kept number for RENORM), ETN_ERR_JSON / ETN_ERR_JSON_DUP = fall back to the reference path,
+ * -1000 - c = CUDA error c.  stats (may be NULL) receives {vectors renormalised on the GPU,
+ * vectors cut as text, embedding arrays seen}. */
+ETN_API int64_t etn_json_truncate_response(const char *json, size_t len, int64_t dims, int mode,
+                                           char *out, size_t out_cap, int n_devices,
+                                           int64_t *stats);
+
+/* "[a,b,c]" -> up to max_n float64 values, correctly rounded like strconv.ParseFloat (the
+ * decoder's number path at handlers.go:2048); numbers past max_n are validated and skipped.
+ * Returns the element count of the array or a negative code. */
+ETN_API int64_t etn_json_parse_array(const char *text, size_t len, double *dst, int64_t max_n);
+
+/* n float64 values -> "[a,b,c]" exactly as encoding/json writes them (helpers.go:14).
+ * Returns bytes written, ETN_ERR_SHAPE if cap is too small (34 bytes per value suffice),
+ * ETN_ERR_JSON for NaN/Inf (which Go's encoder refuses). */
+ETN_API int64_t etn_json_format_array(const double *v, int64_t n, char *buf, size_t cap);
 
 /* ---- bench/test utility ---- */
 

@@ -394,6 +394,8 @@ const char* etn_strerror(int code) {
     case ETN_ERR_ALIGN: return "pointer not aligned to the element size";
     case ETN_ERR_NOT_INIT: return "etn_init has not been called";
     case ETN_ERR_DEVICE: return "bad device list";
+    case ETN_ERR_JSON: return "malformed JSON, non-finite value or number outside float64";
+    case ETN_ERR_JSON_DUP: return "duplicate \"data\" or \"embedding\" key";
     case ETN_ERR_TOO_LARGE: return "batch does not fit the built-in staging array (ETN_STATIC_STAGE_BYTES)";
     default: break;
   }

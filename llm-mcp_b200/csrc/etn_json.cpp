@@ -1,0 +1,398 @@
+// etn_json.cpp — SURVEY.md §8(f) N1: the embedding arrays of an OpenAI-format response go
+// from JSON text straight into a pinned [batch x k] float64 buffer and back out, without the
+// map[string]any round trip the reference pays for (json.NewDecoder(...).Decode(&result),
+// core/internal/api/handlers.go:2047-2050, and json.NewEncoder(w).Encode(payload),
+// core/internal/api/helpers.go:11-15 — every number boxed into an interface value on the way
+// in, every number formatted on the way out, although only the first `dims` of each vector
+// survive).
+//
+// What is parsed and what is not: only the first `dims` numbers of the arrays that are
+// actually cut are ever converted, and only in TRUNCATE_RENORM mode.  In TRUNCATE mode the
+// kept number tokens are copied as text, so they are bit-identical by construction.
+// Everything outside the `data[*].embedding` arrays passes through byte for byte.  (The
+// reference re-encodes the whole map, which sorts object keys and drops insignificant
+// white space: the output here is the same JSON value, not the same bytes.)
+//
+// Numbers: std::from_chars / std::to_chars are correctly rounded and shortest-round-trip, the
+// guarantees Go's strconv.ParseFloat(s, 64) and strconv.AppendFloat(b, f, fmt, -1, 64) give;
+// layout follows encoding/json's floatEncoder: 'f' form unless |x| < 1e-6 or |x| >= 1e21,
+// then 'e' form with "e-0d" shortened to "e-d".
+#include "../../include/embed_truncate_norm.h"
+
+#include <charconv>
+#include <cmath>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+namespace {
+
+struct Scanner {
+  const char* b;
+  const char* e;
+  const char* p;
+  bool ok = true;
+
+  void ws() { while (p < e && (*p == ' ' || *p == '\t' || *p == '\n' || *p == '\r')) ++p; }
+  bool fail() { ok = false; return false; }
+
+  // p at the opening quote; on return p is one past the closing quote.
+  bool skip_string() {
+    if (p >= e || *p != '"') return fail();
+    ++p;
+    while (p < e) {
+      const char c = *p++;
+      if (c == '"') return true;
+      if (c == '\\') { if (p >= e) return fail(); ++p; }
+      else if ((unsigned char)c < 0x20) return fail();
+    }
+    return fail();
+  }
+  // Same, and tells whether the string's raw bytes equal `key` (keys with escapes never match
+  // the plain ASCII keys looked for here; they are reported as a mismatch, which is right
+  // unless someone spells "data" as "data" — that is caught by the caller as a duplicate
+  // only if it matters, and otherwise passes through untouched).
+  bool string_is(const char* key, bool* same) {
+    const char* s = p + 1;
+    if (!skip_string()) return false;
+    const size_t n = (size_t)(p - 1 - s);
+    *same = n == strlen(key) && memcmp(s, key, n) == 0;
+    return true;
+  }
+  bool skip_number() {
+    const char* s = p;
+    if (p < e && *p == '-') ++p;
+    if (p >= e) return fail();
+    if (*p == '0') ++p;
+    else if (*p >= '1' && *p <= '9') { while (p < e && *p >= '0' && *p <= '9') ++p; }
+    else return fail();
+    if (p < e && *p == '.') {
+      ++p;
+      if (p >= e || *p < '0' || *p > '9') return fail();
+      while (p < e && *p >= '0' && *p <= '9') ++p;
+    }
+    if (p < e && (*p == 'e' || *p == 'E')) {
+      ++p;
+      if (p < e && (*p == '+' || *p == '-')) ++p;
+      if (p >= e || *p < '0' || *p > '9') return fail();
+      while (p < e && *p >= '0' && *p <= '9') ++p;
+    }
+    return p > s;
+  }
+  bool skip_literal(const char* lit) {
+    const size_t n = strlen(lit);
+    if ((size_t)(e - p) < n || memcmp(p, lit, n) != 0) return fail();
+    p += n;
+    return true;
+  }
+  bool skip_value(int depth = 0) {
+    if (depth > 512) return fail();
+    ws();
+    if (p >= e) return fail();
+    switch (*p) {
+      case '"': return skip_string();
+      case '{': {
+        ++p; ws();
+        if (p < e && *p == '}') { ++p; return true; }
+        for (;;) {
+          ws();
+          if (!skip_string()) return false;
+          ws();
+          if (p >= e || *p != ':') return fail();
+          ++p;
+          if (!skip_value(depth + 1)) return false;
+          ws();
+          if (p < e && *p == ',') { ++p; continue; }
+          if (p < e && *p == '}') { ++p; return true; }
+          return fail();
+        }
+      }
+      case '[': {
+        ++p; ws();
+        if (p < e && *p == ']') { ++p; return true; }
+        for (;;) {
+          if (!skip_value(depth + 1)) return false;
+          ws();
+          if (p < e && *p == ',') { ++p; continue; }
+          if (p < e && *p == ']') { ++p; return true; }
+          return fail();
+        }
+      }
+      case 't': return skip_literal("true");
+      case 'f': return skip_literal("false");
+      case 'n': return skip_literal("null");
+      default: return skip_number();
+    }
+  }
+};
+
+// One array-valued "embedding" of a data item.
+struct Span {
+  int64_t open;        // offset of '['
+  int64_t close;       // offset one past ']'
+  int64_t count;       // elements
+  int64_t cut;         // offset one past the `dims`-th element (valid when count > dims)
+  bool numeric;        // the first min(count, dims) elements are all JSON numbers
+};
+
+// p at '[' of an embedding array.  Records the span; `dims` bounds the numeric check.
+bool scan_embedding(Scanner& sc, int64_t dims, Span* out) {
+  out->open = sc.p - sc.b;
+  out->count = 0;
+  out->cut = -1;
+  out->numeric = true;
+  ++sc.p; sc.ws();
+  if (sc.p < sc.e && *sc.p == ']') { ++sc.p; out->close = sc.p - sc.b; return true; }
+  for (;;) {
+    sc.ws();
+    if (sc.p >= sc.e) return sc.fail();
+    const char c = *sc.p;
+    const bool is_num = c == '-' || (c >= '0' && c <= '9');
+    if (out->count < dims && !is_num) out->numeric = false;
+    if (is_num) { if (!sc.skip_number()) return false; }
+    else if (!sc.skip_value(2)) return false;
+    ++out->count;
+    if (out->count == dims) out->cut = sc.p - sc.b;
+    sc.ws();
+    if (sc.p < sc.e && *sc.p == ',') { ++sc.p; continue; }
+    if (sc.p < sc.e && *sc.p == ']') { ++sc.p; out->close = sc.p - sc.b; return true; }
+    return sc.fail();
+  }
+}
+
+// Finds the embedding arrays of result["data"][*]["embedding"] (handlers.go:2064-2073).
+// Returns 0, ETN_ERR_JSON for malformed input, ETN_ERR_JSON_DUP when "data" or an item's
+// "embedding" occurs twice (Go keeps the last one and drops the other on re-encode; a splice
+// cannot mimic that, the caller should take the reference path).
+int find_embeddings(const char* json, size_t len, int64_t dims, std::vector<Span>* spans) {
+  Scanner sc{json, json + len, json};
+  sc.ws();
+  if (sc.p >= sc.e || *sc.p != '{') {            // not an object: Go's Decode(&map) would fail earlier
+    if (!sc.skip_value()) return ETN_ERR_JSON;
+    return ETN_OK;
+  }
+  ++sc.p; sc.ws();
+  int data_seen = 0;
+  if (sc.p < sc.e && *sc.p == '}') return ETN_OK;
+  for (;;) {
+    sc.ws();
+    bool is_data = false;
+    if (!sc.string_is("data", &is_data)) return ETN_ERR_JSON;
+    sc.ws();
+    if (sc.p >= sc.e || *sc.p != ':') return ETN_ERR_JSON;
+    ++sc.p; sc.ws();
+    if (is_data && ++data_seen > 1) return ETN_ERR_JSON_DUP;
+    if (is_data && sc.p < sc.e && *sc.p == '[') {
+      ++sc.p; sc.ws();
+      if (sc.p < sc.e && *sc.p == ']') { ++sc.p; }
+      else for (;;) {
+        sc.ws();
+        if (sc.p < sc.e && *sc.p == '{') {       // a data item: look for its "embedding"
+          ++sc.p; sc.ws();
+          int emb_seen = 0;
+          if (sc.p < sc.e && *sc.p == '}') { ++sc.p; }
+          else for (;;) {
+            sc.ws();
+            bool is_emb = false;
+            if (!sc.string_is("embedding", &is_emb)) return ETN_ERR_JSON;
+            sc.ws();
+            if (sc.p >= sc.e || *sc.p != ':') return ETN_ERR_JSON;
+            ++sc.p; sc.ws();
+            if (is_emb && ++emb_seen > 1) return ETN_ERR_JSON_DUP;
+            if (is_emb && sc.p < sc.e && *sc.p == '[') {
+              Span s;
+              if (!scan_embedding(sc, dims, &s)) return ETN_ERR_JSON;
+              spans->push_back(s);
+            } else if (!sc.skip_value(2)) return ETN_ERR_JSON;
+            sc.ws();
+            if (sc.p < sc.e && *sc.p == ',') { ++sc.p; continue; }
+            if (sc.p < sc.e && *sc.p == '}') { ++sc.p; break; }
+            return ETN_ERR_JSON;
+          }
+        } else if (!sc.skip_value(1)) return ETN_ERR_JSON;   // non-object item: skipped (:2069-2072)
+        sc.ws();
+        if (sc.p < sc.e && *sc.p == ',') { ++sc.p; continue; }
+        if (sc.p < sc.e && *sc.p == ']') { ++sc.p; break; }
+        return ETN_ERR_JSON;
+      }
+    } else if (!sc.skip_value(1)) return ETN_ERR_JSON;
+    sc.ws();
+    if (sc.p < sc.e && *sc.p == ',') { ++sc.p; continue; }
+    if (sc.p < sc.e && *sc.p == '}') { ++sc.p; break; }
+    return ETN_ERR_JSON;
+  }
+  sc.ws();
+  return sc.p == sc.e ? ETN_OK : ETN_ERR_JSON;
+}
+
+// encoding/json floatEncoder for float64.  Returns the number of bytes written (<= 32).
+size_t format_go_float(double f, char* out) {
+  char* o = out;
+  if (f == 0) {                                   // "0" or "-0"
+    if (std::signbit(f)) *o++ = '-';
+    *o++ = '0';
+    return (size_t)(o - out);
+  }
+  char sci[40];
+  auto r = std::to_chars(sci, sci + sizeof sci, f, std::chars_format::scientific);   // d[.ddd]e[+-]XX
+  const char* s = sci;
+  if (*s == '-') { *o++ = '-'; ++s; }
+  const char* ep = s;
+  while (ep < r.ptr && *ep != 'e') ++ep;
+  char digits[24];
+  int nd = 0;
+  for (const char* q = s; q < ep; ++q) if (*q != '.') digits[nd++] = *q;
+  int exp10 = 0;
+  std::from_chars(ep + 1 + (ep[1] == '+'), r.ptr, exp10);
+  const double a = std::fabs(f);
+  if (a < 1e-6 || a >= 1e21) {                    // 'e' form: d[.ddd]e[+-]dd, then e-0d -> e-d
+    *o++ = digits[0];
+    if (nd > 1) { *o++ = '.'; for (int i = 1; i < nd; ++i) *o++ = digits[i]; }
+    *o++ = 'e';
+    *o++ = exp10 < 0 ? '-' : '+';
+    const int ax = exp10 < 0 ? -exp10 : exp10;
+    if (ax < 10) { if (exp10 >= 0) *o++ = '0'; *o++ = (char)('0' + ax); }   // "e+07" stays, "e-07" -> "e-7"
+    else { auto t = std::to_chars(o, o + 8, ax); o = t.ptr; }
+    return (size_t)(o - out);
+  }
+  // 'f' form, shortest digits, no exponent
+  if (exp10 < 0) {
+    *o++ = '0'; *o++ = '.';
+    for (int i = 0; i < -exp10 - 1; ++i) *o++ = '0';
+    for (int i = 0; i < nd; ++i) *o++ = digits[i];
+  } else {
+    for (int i = 0; i <= exp10; ++i) *o++ = i < nd ? digits[i] : '0';
+    if (nd > exp10 + 1) { *o++ = '.'; for (int i = exp10 + 1; i < nd; ++i) *o++ = digits[i]; }
+  }
+  return (size_t)(o - out);
+}
+
+// Reusable pinned staging for the rewrite (one per thread would be better still; handlers
+// call concurrently, so a mutex guards the shared one and overflow callers allocate their own).
+struct PinPool {
+  std::mutex mu;
+  void* in = nullptr;
+  size_t cap = 0;
+} g_pin;
+
+}  // namespace
+
+extern "C" {
+
+int64_t etn_json_format_array(const double* v, int64_t n, char* buf, size_t cap) {
+  if (n < 0 || (!v && n > 0) || !buf) return ETN_ERR_NULL;
+  size_t o = 0;
+  if (cap < 2) return ETN_ERR_SHAPE;
+  buf[o++] = '[';
+  for (int64_t i = 0; i < n; ++i) {
+    if (o + 34 > cap) return ETN_ERR_SHAPE;
+    if (i) buf[o++] = ',';
+    if (!std::isfinite(v[i])) return ETN_ERR_JSON;   // Go's encoder refuses NaN/Inf (helpers.go:14 drops the body)
+    o += format_go_float(v[i], buf + o);
+  }
+  if (o + 1 > cap) return ETN_ERR_SHAPE;
+  buf[o++] = ']';
+  return (int64_t)o;
+}
+
+int64_t etn_json_parse_array(const char* text, size_t len, double* dst, int64_t max_n) {
+  if (!text || (!dst && max_n > 0)) return ETN_ERR_NULL;
+  Scanner sc{text, text + len, text};
+  sc.ws();
+  if (sc.p >= sc.e || *sc.p != '[') return ETN_ERR_JSON;
+  ++sc.p; sc.ws();
+  int64_t n = 0;
+  if (sc.p < sc.e && *sc.p == ']') return 0;
+  for (;;) {
+    sc.ws();
+    const char* s = sc.p;
+    if (!sc.skip_number()) return ETN_ERR_JSON;
+    if (n < max_n) {
+      auto r = std::from_chars(s, sc.p, dst[n]);
+      if (r.ec == std::errc::result_out_of_range) return ETN_ERR_JSON;    // Go: "cannot unmarshal number ... into float64"
+      if (r.ec != std::errc() || r.ptr != sc.p) return ETN_ERR_JSON;
+    }
+    ++n;
+    sc.ws();
+    if (sc.p < sc.e && *sc.p == ',') { ++sc.p; continue; }
+    if (sc.p < sc.e && *sc.p == ']') return n;
+    return ETN_ERR_JSON;
+  }
+}
+
+int64_t etn_json_truncate_response(const char* json, size_t len, int64_t dims, int mode, char* out,
+                                   size_t out_cap, int n_devices, int64_t* stats) {
+  if (mode != ETN_TRUNCATE && mode != ETN_TRUNCATE_RENORM) return ETN_ERR_ENUM;
+  if (!json || !out) return ETN_ERR_NULL;
+  if (stats) { stats[0] = stats[1] = stats[2] = 0; }
+  std::vector<Span> spans;
+  if (dims > 0) {
+    const int rc = find_embeddings(json, len, dims, &spans);
+    if (rc != ETN_OK) return rc;
+  }
+  // vectors that go through the GPU: longer than dims, numeric prefix, renorm requested
+  std::vector<size_t> gpu;
+  if (mode == ETN_TRUNCATE_RENORM)
+    for (size_t i = 0; i < spans.size(); ++i)
+      if (spans[i].count > dims && spans[i].numeric) gpu.push_back(i);
+  double* vals = nullptr;
+  void* own = nullptr;
+  std::unique_lock<std::mutex> pin_lock(g_pin.mu, std::defer_lock);
+  if (!gpu.empty()) {
+    const size_t need = gpu.size() * (size_t)dims * sizeof(double);
+    if (pin_lock.try_lock()) {
+      if (g_pin.cap < need) {
+        etn_free_pinned(g_pin.in);
+        g_pin.in = etn_alloc_pinned(need);
+        g_pin.cap = g_pin.in ? need : 0;
+      }
+      vals = (double*)g_pin.in;
+      if (!vals) pin_lock.unlock();
+    }
+    if (!vals) { own = etn_alloc_pinned(need); vals = (double*)own; }
+    if (!vals) return 2;                           // cudaErrorMemoryAllocation
+    for (size_t g = 0; g < gpu.size(); ++g) {
+      const Span& s = spans[gpu[g]];
+      const int64_t n = etn_json_parse_array(json + s.open, (size_t)(s.close - s.open), vals + g * dims, dims);
+      if (n < 0) { if (own) etn_free_pinned(own); return n; }
+    }
+    // prefix-only buffer: D == k == dims, renormalised in place through the host path
+    const int rc = embed_truncate_norm_host((int64_t)gpu.size(), dims, dims, ETN_F64, ETN_TRUNCATE_RENORM, vals, 0,
+                                            vals, n_devices);
+    if (rc != 0) { if (own) etn_free_pinned(own); return rc < 0 ? rc : -1000 - rc; }
+  }
+  // splice
+  size_t o = 0, src = 0, g = 0;
+  auto put = [&](const char* p, size_t n) -> bool {
+    if (o + n > out_cap) return false;
+    memcpy(out + o, p, n);
+    o += n;
+    return true;
+  };
+  bool fits = true;
+  for (size_t i = 0; i < spans.size() && fits; ++i) {
+    const Span& s = spans[i];
+    if (s.count <= dims) continue;                 // left whole, never padded (handlers.go:2074)
+    fits = put(json + src, (size_t)s.open - src);
+    if (!fits) break;
+    if (g < gpu.size() && gpu[g] == i) {
+      const int64_t w = etn_json_format_array(vals + g * dims, dims, out + o, out_cap - o);
+      if (w < 0) { fits = w != ETN_ERR_SHAPE; if (fits) { if (own) etn_free_pinned(own); return w; } break; }
+      o += (size_t)w;
+      ++g;
+      if (stats) ++stats[0];
+    } else {                                       // the reference reslice, on the text: tokens kept verbatim
+      fits = put(json + s.open, (size_t)(s.cut - s.open)) && put("]", 1);
+      if (stats) ++stats[1];
+    }
+    src = (size_t)s.close;
+  }
+  if (fits) fits = put(json + src, len - src);
+  if (own) etn_free_pinned(own);
+  if (!fits) return ETN_ERR_SHAPE;
+  if (stats) stats[2] = (int64_t)spans.size();
+  return (int64_t)o;
+}
+
+}  // extern "C"

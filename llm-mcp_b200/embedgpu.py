@@ -28,6 +28,7 @@ LIB_PATH = os.path.join(_PKG, "libembed_truncate_norm.so")
 F32, F64 = 0, 1
 TRUNCATE, TRUNCATE_RENORM = 0, 1
 ERR_NULL, ERR_SHAPE, ERR_ENUM, ERR_ALIGN, ERR_NOT_INIT, ERR_DEVICE, ERR_TOO_LARGE = -1, -2, -3, -4, -5, -6, -7
+ERR_JSON, ERR_JSON_DUP = -8, -9
 STATIC_STAGE_BYTES = 16 << 20
 
 EXPORTS = (
@@ -35,6 +36,7 @@ EXPORTS = (
     "embed_truncate_norm_ragged", "etn_init", "etn_shutdown", "etn_device_count",
     "etn_alloc_pinned", "etn_free_pinned", "embed_truncate_norm_host", "etn_fill_synthetic",
     "embed_truncate_norm_host_static",
+    "etn_json_truncate_response", "etn_json_parse_array", "etn_json_format_array",
 )
 
 
@@ -73,6 +75,12 @@ def lib() -> ctypes.CDLL:
         L.embed_truncate_norm_host.argtypes = [i64, i64, i64, ci, ci, vp, i64, vp, ci]
         L.etn_fill_synthetic.argtypes = [ctypes.c_uint64, i64, i64, i64, i64, i64, ci, vp, vp]
         L.embed_truncate_norm_host_static.argtypes = [i64, i64, i64, ci, ci, vp, i64, vp, vp]
+        L.etn_json_truncate_response.argtypes = [ctypes.c_char_p, ctypes.c_size_t, i64, ci, vp, ctypes.c_size_t, ci, vp]
+        L.etn_json_truncate_response.restype = i64
+        L.etn_json_parse_array.argtypes = [ctypes.c_char_p, ctypes.c_size_t, vp, i64]
+        L.etn_json_parse_array.restype = i64
+        L.etn_json_format_array.argtypes = [vp, i64, vp, ctypes.c_size_t]
+        L.etn_json_format_array.restype = i64
         _lib = L
     return _lib
 
@@ -268,3 +276,23 @@ def shard_ragged(k_per_row, D: int, world: int) -> list[tuple[int, int]]:
     cuts.append(n)
     cuts = np.maximum.accumulate(np.minimum(cuts, n))
     return [(int(cuts[g]), int(cuts[g + 1])) for g in range(world)]
+
+
+# ------------------------------------------------------------------ JSON packer (N1) ----
+def truncate_response_json(body: bytes, dims: int, renorm: bool | None = None, n_devices: int = 0):
+    """etn_json_truncate_response: the provider's response text in, the handler's response
+    text out, with the embedding arrays cut (and, with renorm, renormalised on the GPU)
+    without ever building the decoded map (handlers.go:2047-2050 / helpers.go:11-15).
+    Returns (bytes, stats).  Raises EtnError with ERR_JSON / ERR_JSON_DUP when the caller
+    should take the reference path instead."""
+    if renorm is None:
+        renorm = renorm_enabled()
+    mode = TRUNCATE_RENORM if renorm else TRUNCATE
+    cap = len(body) + 2 if not renorm else len(body) + 2 + 26 * max(dims, 0) * (body.count(b'"embedding"') + 1)
+    out = ctypes.create_string_buffer(cap)
+    stats = (ctypes.c_int64 * 3)()
+    n = lib().etn_json_truncate_response(body, len(body), dims, mode, out, cap, n_devices, stats)
+    if n < 0:
+        code = int(n) if n > -1000 else int(-1000 - n)
+        raise EtnError(code, strerror(code), "etn_json_truncate_response")
+    return out.raw[:n], {"gpu_vectors": stats[0], "resliced_vectors": stats[1], "arrays": stats[2]}

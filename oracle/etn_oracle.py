@@ -204,3 +204,57 @@ def _go_atoi(s: str) -> int:
     if not -(1 << 63) <= n < (1 << 63):
         raise ValueError(s)
     return n
+
+
+# ---------------------------------------------------------------------------
+# encoding/json number formatting and the response-level restatement (N1 oracle)
+# ---------------------------------------------------------------------------
+
+def go_format_float(x: float) -> str:
+    """encoding/json's floatEncoder for float64 (Go 1.22 encode.go): strconv.AppendFloat with
+    the shortest round-trip digits, format 'f' unless |x| < 1e-6 or |x| >= 1e21, then 'e' with
+    a two-digit negative exponent "e-0d" shortened to "e-d".  Restated from Python's repr,
+    which yields the same shortest digit string."""
+    import math
+    from decimal import Decimal
+    if math.isnan(x) or math.isinf(x):
+        raise ValueError("json: unsupported value")
+    if x == 0:
+        return "-0" if math.copysign(1.0, x) < 0 else "0"
+    sign, digits, exp = Decimal(repr(x)).as_tuple()
+    digits = list(digits)
+    while len(digits) > 1 and digits[-1] == 0:
+        digits.pop(); exp += 1
+    ds = "".join(map(str, digits))
+    e10 = exp + len(ds) - 1                      # decimal exponent of the first digit
+    neg = "-" if sign else ""
+    a = abs(x)
+    if a < 1e-6 or a >= 1e21:
+        mant = ds[0] + ("." + ds[1:] if len(ds) > 1 else "")
+        ax = abs(e10)
+        es = ("-" if e10 < 0 else "+") + (str(ax) if (ax >= 10 or e10 < 0) else "0" + str(ax))
+        return f"{neg}{mant}e{es}"
+    if e10 < 0:
+        return neg + "0." + "0" * (-e10 - 1) + ds
+    if len(ds) <= e10 + 1:
+        return neg + ds + "0" * (e10 + 1 - len(ds))
+    return neg + ds[:e10 + 1] + "." + ds[e10 + 1:]
+
+
+def response_ref(body: bytes, dims: int, renorm: bool):
+    """What the handler returns, as a decoded value: json.Decode (handlers.go:2047-2050),
+    truncateEmbeddings when dims > 0 (:1891-1893), and — only with renorm — the exact
+    renormalisation of every cut vector made of numbers."""
+    import json
+    result = json.loads(body)
+    if dims > 0:
+        before = {id(it): len(it["embedding"]) for it in result.get("data", []) if isinstance(result.get("data"), list)
+                  and isinstance(it, dict) and isinstance(it.get("embedding"), list)} if isinstance(result, dict) else {}
+        truncate_embeddings_ref(result, dims)
+        if renorm and isinstance(result, dict) and isinstance(result.get("data"), list):
+            for it in result["data"]:
+                if isinstance(it, dict) and isinstance(it.get("embedding"), list) and before.get(id(it), 0) > dims \
+                        and all(type(v) in (int, float) for v in it["embedding"]):
+                    v = np.array([[float(t) for t in it["embedding"]]], dtype=np.float64)
+                    it["embedding"] = renorm_exact(v, dims)[0].tolist()
+    return result

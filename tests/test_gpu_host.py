@@ -3,6 +3,7 @@ mirror of the reference call site, truncate_embeddings(result, dims)
 (reference: core/internal/api/handlers.go:1891-1893, 2062-2078)."""
 import copy
 import json
+import json
 
 import numpy as np
 import pytest
@@ -131,3 +132,31 @@ def test_host_path_row_sharded_over_devices(oracle):
         got = eg.truncate_norm_host(xh, k, eg.TRUNCATE_RENORM, n_devices=nd)
         _ulp(oracle, got, want)
     assert eg.lib().embed_truncate_norm_host(4, 8, 4, eg.F32, 1, xh.ctypes.data, 0, xh.ctypes.data, n + 1) == eg.ERR_DEVICE
+
+
+# ------------------------------------------------------------- JSON packer (N1) ----
+def test_json_packer_renorm_against_reference(oracle):
+    """Response text in, response text out: cut vectors are parsed prefix-only into pinned
+    memory, renormalised on the GPU and formatted the way encoding/json writes float64."""
+    import re
+    x = oracle.fill(1, 48, 4096, np.float64)
+    data = [{"object": "embedding", "index": i, "embedding": r.tolist()} for i, r in enumerate(x)]
+    data[5]["embedding"] = data[5]["embedding"][:700]            # shorter than dims: left whole
+    data[6]["embedding"] = "base64=="                             # not an array
+    data[7]["embedding"] = data[7]["embedding"][:1023] + ["x"] + data[7]["embedding"][1024:]   # unpackable: cut only
+    data[8]["embedding"] = [0.0] * 2000                           # zero prefix: copied, no NaN
+    body = json.dumps({"object": "list", "data": data, "usage": {"prompt_tokens": 3}}).encode()
+    out, stats = eg.truncate_response_json(body, 1024, renorm=True)
+    got, want = json.loads(out), oracle.response_ref(body, 1024, renorm=True)
+    assert stats == {"gpu_vectors": 45, "resliced_vectors": 1, "arrays": 47}
+    assert got["usage"] == want["usage"] and len(got["data"]) == len(want["data"])
+    for a, b in zip(got["data"], want["data"]):
+        assert a.keys() == b.keys() and a["index"] == b["index"]
+        if isinstance(b["embedding"], list) and all(type(v) is float for v in b["embedding"]):
+            _ulp(oracle, np.array(a["embedding"], dtype=np.float64), np.array(b["embedding"], dtype=np.float64))
+        else:
+            assert a["embedding"] == b["embedding"]
+    # every number the packer wrote is encoding/json's spelling of the value it parses back to
+    m = re.search(rb'"index": 0, "embedding": \[([^\]]*)\]|"embedding": \[([^\]]*)\], "index": 0', out)
+    toks = (m.group(1) or m.group(2)).decode().split(",")
+    assert len(toks) == 1024 and all(t == oracle.go_format_float(float(t)) for t in toks)

@@ -1,0 +1,127 @@
+"""CPU tests of the JSON packer: number parsing/formatting against
+encoding/json's rules, and the response rewrite in TRUNCATE mode (no GPU involved: the kept
+tokens are spliced as text) against the map-level restatement of the reference
+(handlers.go:2047-2050, 2062-2078; helpers.go:11-15)."""
+import ctypes
+import json
+import math
+import struct
+
+import numpy as np
+import pytest
+
+from llm_mcp_b200 import embedgpu as eg
+
+# encoding/json outputs that are part of Go's documented/observable behaviour
+GO_KNOWN = [
+    (0.1, "0.1"), (100.0, "100"), (1.5, "1.5"), (-0.0, "-0"), (0.0, "0"), (123456789.0, "123456789"),
+    (1e-6, "0.000001"), (1e-7, "1e-7"), (1.234e-7, "1.234e-7"), (1e-10, "1e-10"), (0.000001234, "0.000001234"),
+    (1e20, "100000000000000000000"), (1e21, "1e+21"), (1.5e300, "1.5e+300"), (5e-324, "5e-324"),
+    (1.7976931348623157e308, "1.7976931348623157e+308"), (-2.5e-9, "-2.5e-9"), (0.30000000000000004, "0.30000000000000004"),
+    (123456789012345680000.0, "123456789012345680000"), (3.0e-5, "0.00003"), (-1234.5678, "-1234.5678"),
+]
+
+
+def fmt(vals):
+    v = np.ascontiguousarray(vals, dtype=np.float64)
+    buf = ctypes.create_string_buffer(34 * len(v) + 2)
+    n = eg.lib().etn_json_format_array(v.ctypes.data, len(v), buf, len(buf))
+    assert n > 0, n
+    return buf.raw[:n].decode()
+
+
+def parse(text, max_n):
+    dst = np.full(max_n, np.nan)
+    n = eg.lib().etn_json_parse_array(text.encode(), len(text.encode()), dst.ctypes.data, max_n)
+    return n, dst
+
+
+def test_format_matches_go_known_answers(oracle):
+    for x, want in GO_KNOWN:
+        assert oracle.go_format_float(x) == want, (x, oracle.go_format_float(x))
+        assert fmt([x]) == f"[{want}]", (x, fmt([x]))
+    assert fmt([]) == "[]" and fmt([1.0, -2.0, 0.5]) == "[1,-2,0.5]"
+    bad = np.array([1.0, np.inf])
+    buf = ctypes.create_string_buffer(100)
+    assert eg.lib().etn_json_format_array(bad.ctypes.data, 2, buf, 100) == eg.ERR_JSON
+    assert eg.lib().etn_json_format_array(bad.ctypes.data, 1, buf, 3) == eg.ERR_SHAPE
+
+
+def test_format_random_doubles_round_trip_and_match_restatement(oracle):
+    rng = np.random.default_rng(3)
+    bits = rng.integers(0, 2**63 - 1, size=20000, dtype=np.int64) | (rng.integers(0, 2, size=20000, dtype=np.int64) << 63)
+    x = bits.view(np.float64)
+    x = x[np.isfinite(x)]
+    x = np.concatenate([x, rng.standard_normal(5000) * 0.03, np.float64(10.0) ** rng.integers(-30, 30, 500),
+                        np.array([9.999999e-7, 1.0000001e-6, 9.99999999999999e20, 1.0000000000000001e21, 2.2250738585072014e-308])])
+    toks = fmt(x)[1:-1].split(",")
+    assert len(toks) == len(x)
+    for v, t in zip(x[::7], toks[::7]):
+        assert t == oracle.go_format_float(float(v)), (v, t)
+    back = np.array([float(t) for t in toks])
+    assert np.array_equal(back.view(np.uint64), x.view(np.uint64))          # shortest digits round-trip exactly
+    n, got = parse("[" + ",".join(toks) + "]", len(x))
+    assert n == len(x) and np.array_equal(got.view(np.uint64), x.view(np.uint64))
+
+
+def test_parse_is_correctly_rounded_and_strict():
+    texts = ["0.1", "1e-7", "-0", "123456789012345678901234567890", "2.2250738585072011e-308", "4.9e-324", "1E5", "0.30000000000000004",
+             "179769313486231570000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000"]
+    n, got = parse("[" + ", ".join(texts) + " ]", len(texts))
+    assert n == len(texts)
+    assert np.array_equal(got.view(np.uint64), np.array([float(t) for t in texts]).view(np.uint64))
+    assert parse("[1,2,3,4]", 2)[0] == 4 and parse("[]", 4)[0] == 0
+    for bad in ("[1,]", "[01]", "[1.]", "[.5]", "[1e]", "[+1]", "[NaN]", "[1 2]", "1,2", "[1e999]", '["x"]'):
+        assert parse(bad, 4)[0] == eg.ERR_JSON, bad
+
+
+def _body(vectors, extra_items=(), **top):
+    data = [{"object": "embedding", "index": i, "embedding": v} for i, v in enumerate(vectors)] + list(extra_items)
+    d = {"object": "list", "data": data, "model": "qwen/qwen3-embedding-8b", "usage": {"prompt_tokens": 5, "total_tokens": 5}}
+    d.update(top)
+    return json.dumps(d).encode()
+
+
+def test_truncate_mode_equals_reference_value_and_keeps_tokens(oracle):
+    rng = np.random.default_rng(8)
+    vecs = [list(map(float, rng.standard_normal(n) * 0.05)) for n in (40, 40, 7, 16, 17)]
+    body = _body(vecs, extra_items=["not-a-map", {"embedding": "AAAA"}, {"embedding": None}, {"index": 9},
+                                    {"embedding": [1, "x", 3.5, None, {"a": [1, 2]}, 6]}], note="<&> é \\\" ]} [")
+    out, stats = eg.truncate_response_json(body, 16, renorm=False)
+    assert json.loads(out) == oracle.response_ref(body, 16, renorm=False)
+    assert stats == {"gpu_vectors": 0, "resliced_vectors": 3, "arrays": 6}
+    # the kept numbers are the provider's own tokens, byte for byte
+    for v in vecs[:2]:
+        kept = json.dumps(v[:16])[1:-1].encode()
+        assert kept in out
+    # short vectors and everything else untouched: nothing but the cut tails went missing
+    assert out.count(b'"embedding"') == body.count(b'"embedding"')
+    for dims in (0, -3):
+        assert eg.truncate_response_json(body, dims, renorm=False)[0] == body
+    assert eg.truncate_response_json(body, 1000, renorm=False)[0] == body
+
+
+def test_rewrite_handles_whitespace_escapes_and_odd_shapes(oracle):
+    body = b' {\n "data" : [ { "index":0 , "embedding" : [ 1.0 , 2.5e-3,\t-7 , 4 ] , "k\\"ey":"]}" } , [1,2,3], {"embedding":[ ]} ],\n "data2":{"embedding":[1,2,3]} }\n'
+    out, _ = eg.truncate_response_json(body, 2, renorm=False)
+    assert json.loads(out) == oracle.response_ref(body, 2, renorm=False)
+    assert b"[ 1.0 , 2.5e-3]" in out                       # tokens and their spacing kept
+    for b2 in (b'{"data": 3}', b'{"data": {"embedding": [1,2,3]}}', b'{}', b'[1,2,3]', b'{"x": {"data": [{"embedding": [1,2,3]}]}}'):
+        assert eg.truncate_response_json(b2, 1, renorm=False)[0] == b2
+    for bad, code in ((b'{"data": [', eg.ERR_JSON), (b'{"data": [{"embedding": [1,2}]}', eg.ERR_JSON), (b'{"a":1} x', eg.ERR_JSON),
+                      (b'{"data": [], "data": []}', eg.ERR_JSON_DUP), (b'{"data": [{"embedding": [1], "embedding": [2]}]}', eg.ERR_JSON_DUP)):
+        with pytest.raises(eg.EtnError) as ei:
+            eg.truncate_response_json(bad, 1, renorm=False)
+        assert ei.value.code == code, bad
+    small = ctypes.create_string_buffer(4)
+    assert eg.lib().etn_json_truncate_response(b'{"a": 1}', 8, 1, 0, small, 4, 0, None) == eg.ERR_SHAPE
+
+
+def test_c1_sized_response_truncate(oracle):
+    """The reference's CPU-runnable case: 1,024 vectors of 4096 numbers cut to 1024."""
+    x = oracle.fill(1, 64, 4096, np.float64)               # 64 vectors keep the CPU suite quick
+    body = _body([r.tolist() for r in x])
+    out, stats = eg.truncate_response_json(body, 1024, renorm=False)
+    got = json.loads(out)
+    assert [len(d["embedding"]) for d in got["data"]] == [1024] * 64 and stats["resliced_vectors"] == 64
+    assert np.array_equal(np.array([d["embedding"] for d in got["data"]]), x[:, :1024])
