@@ -3,7 +3,6 @@ mirror of the reference call site, truncate_embeddings(result, dims)
 (reference: core/internal/api/handlers.go:1891-1893, 2062-2078)."""
 import copy
 import json
-import json
 
 import numpy as np
 import pytest
