@@ -172,10 +172,10 @@ def run_reference(args, wl, rank):
 # ------------------------------------------------------------------ GPU arm ----
 # kernel the library's dispatcher (csrc/etn_api.cu launch_dense) picks per workload
 KERNELS = {
-    "c1": "etn::rows_reg_kernel<double, VB=32, NV=8, R=1, L=32> (8 KiB rows, one warp per row)",
+    "c1": "etn::rows_bulk_kernel<double, NV16=16, S=2, NCW=4> (8 KiB rows, bulk-async ring, one row per warp)",
     "c2": "etn::rows_reg_kernel<float, VB=32, NV=1, R=4, L=32> (1 KiB rows, four rows per warp)",
     "c3": "etn::rows_reg_kernel<float, VB=32, NV=4, R=1, L=32> (4 KiB rows, one warp per row)",
-    "c3f64": "etn::rows_reg_kernel<double, VB=32, NV=8, R=1, L=32> (8 KiB rows, one warp per row)",
+    "c3f64": "etn::rows_bulk_kernel<double, NV16=16, S=2, NCW=4> (8 KiB rows, bulk-async ring, 4 rows per warp)",
     "c4": "etn::rows_reg_kernel<float, VB=32, NV=1, R=4, L=32> (1 KiB rows, four rows per warp)",
 }
 
@@ -253,6 +253,7 @@ def run_ours(args, wl, rank, local_rank, world):
         step(i)
     sampler = ClockSampler(physical_gpu_index(local_rank))
     barrier()
+    launches0 = eg.counters()["llmcore_embed_gpu_kernel_launches_total"]
     sampler.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
@@ -261,6 +262,7 @@ def run_ours(args, wl, rank, local_rank, world):
     ev1.record()
     barrier()
     clocks = sampler.stop()
+    gpu_launches = eg.counters()["llmcore_embed_gpu_kernel_launches_total"] - launches0   # counted by the library
     ms = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
@@ -348,7 +350,7 @@ def run_ours(args, wl, rank, local_rank, world):
                      "algorithmic_bytes_per_launch": algo_bytes, "kernel": KERNELS.get(args.workload)},
         "clocks": clocks,
         "e2e": e2e,
-        "gpu_launches": args.steps,
+        "gpu_launches": gpu_launches,
         "cpu_baseline": cpu,
         "other_workloads": others,
     }

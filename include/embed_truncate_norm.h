@@ -195,6 +195,24 @@ ETN_API int64_t etn_json_parse_array(const char *text, size_t len, double *dst, 
  * ETN_ERR_JSON for NaN/Inf (which Go's encoder refuses). */
 ETN_API int64_t etn_json_format_array(const double *v, int64_t n, char *buf, size_t cap);
 
+/* ---- observability ---- */
+
+/* Cumulative process-wide counters, to be exported as Prometheus counters beside
+ * llmcore_embedding_requests_total and friends (core/internal/metrics/metrics.go:9-26,
+ * registered at :63-70).  Index = ETN_CTR_*; etn_counter_name gives the metric name.
+ * etn_get_counters writes min(capacity, ETN_CTR_COUNT) values and returns that number. */
+#define ETN_CTR_DEVICE_CALLS 0    /* embed_truncate_norm / embed_truncate / _ragged calls */
+#define ETN_CTR_DEVICE_ROWS 1     /* rows those calls covered */
+#define ETN_CTR_KERNEL_LAUNCHES 2 /* kernels this library launched */
+#define ETN_CTR_HOST_CALLS 3      /* embed_truncate_norm_host calls */
+#define ETN_CTR_HOST_ROWS 4
+#define ETN_CTR_H2D_BYTES 5       /* bytes copied host -> device by the host path */
+#define ETN_CTR_D2H_BYTES 6
+#define ETN_CTR_ERRORS 7          /* non-zero returns (the handler then serves the reslice) */
+#define ETN_CTR_COUNT 8
+ETN_API int etn_get_counters(int64_t *out, int capacity);
+ETN_API const char *etn_counter_name(int index);
+
 /* ---- bench/test utility ---- */
 
 /* Writes the synthetic matrix of SURVEY.md §8(d) (as amended in DESIGN.md: signed 24-bit

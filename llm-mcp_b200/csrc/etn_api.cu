@@ -22,6 +22,20 @@ using namespace etn;
 
 inline bool aligned_to(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
 
+// ---------------------------------------------------------------- counters ----
+// Cumulative, process-wide; the Go side exports them next to the embedding collectors of
+// core/internal/metrics/metrics.go:9-26.  Order = ETN_CTR_* in the header.
+std::atomic<int64_t> g_ctr[ETN_CTR_COUNT];
+inline void count(int i, int64_t v = 1) { g_ctr[i].fetch_add(v, std::memory_order_relaxed); }
+inline int counted_launch(cudaError_t e) {
+  if (e == cudaSuccess) count(ETN_CTR_KERNEL_LAUNCHES);
+  return (int)e;
+}
+inline int finish(int rc) {
+  if (rc != 0) count(ETN_CTR_ERRORS);
+  return rc;
+}
+
 // ------------------------------------------------------------ device info ----
 struct DeviceInfo {
   std::atomic<int> sms{0};
@@ -81,7 +95,7 @@ int launch_kernel(void (*kern)(KArgs...), int grid, cudaStream_t s, Args... args
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
-  return (int)cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+  return counted_launch(cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...));
 }
 
 // MINB = resident blocks per SM the register allocation is held to.
@@ -141,8 +155,8 @@ int launch_bulk(const void* in, void* out, int64_t batch, int64_t in_pitch, int 
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
-  return (int)cudaLaunchKernelEx(&cfg, kern, (const char*)in, (char*)out, batch, in_pitch, nvec16, rpw, D,
-                                 k_per_row, out_offsets);
+  return counted_launch(cudaLaunchKernelEx(&cfg, kern, (const char*)in, (char*)out, batch, in_pitch, nvec16, rpw,
+                                           D, k_per_row, out_offsets));
 }
 
 template <typename T, int MODE>
@@ -259,8 +273,8 @@ int launch_ragged(const void* in, void* out, int64_t batch, int64_t D, const int
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
-  return (int)cudaLaunchKernelEx(&cfg, kern, (const char*)in, (char*)out, batch, in_pitch, rpw, D, k_per_row,
-                                 out_offsets);
+  return counted_launch(cudaLaunchKernelEx(&cfg, kern, (const char*)in, (char*)out, batch, in_pitch, rpw, D,
+                                           k_per_row, out_offsets));
 }
 
 int check_dense(int64_t batch, int64_t D, int64_t k, int dtype, const void* in, const void* out) {
@@ -407,14 +421,16 @@ int embed_truncate_norm(int64_t batch, int64_t D, int64_t k, int dtype, const vo
                         void* stream) {
   if (int rc = check_dense(batch, D, k, dtype, in, out)) return rc;
   if (batch == 0) return ETN_OK;
-  return run_dense(batch, D, k, dtype, ETN_TRUNCATE_RENORM, in, out, (cudaStream_t)stream);
+  count(ETN_CTR_DEVICE_CALLS); count(ETN_CTR_DEVICE_ROWS, batch);
+  return finish(run_dense(batch, D, k, dtype, ETN_TRUNCATE_RENORM, in, out, (cudaStream_t)stream));
 }
 
 int embed_truncate(int64_t batch, int64_t D, int64_t k, int dtype, const void* in, void* out,
                    void* stream) {
   if (int rc = check_dense(batch, D, k, dtype, in, out)) return rc;
   if (batch == 0) return ETN_OK;
-  return run_dense(batch, D, k, dtype, ETN_TRUNCATE, in, out, (cudaStream_t)stream);
+  count(ETN_CTR_DEVICE_CALLS); count(ETN_CTR_DEVICE_ROWS, batch);
+  return finish(run_dense(batch, D, k, dtype, ETN_TRUNCATE, in, out, (cudaStream_t)stream));
 }
 
 int embed_truncate_norm_ragged(int64_t batch, int64_t D, const int32_t* k_per_row,
@@ -430,11 +446,12 @@ int embed_truncate_norm_ragged(int64_t batch, int64_t D, const int32_t* k_per_ro
       !aligned_to(out_offsets, 8))
     return ETN_ERR_ALIGN;
   cudaStream_t s = (cudaStream_t)stream;
+  count(ETN_CTR_DEVICE_CALLS); count(ETN_CTR_DEVICE_ROWS, batch);
   if (mode == ETN_TRUNCATE)
-    return dtype == ETN_F32 ? launch_ragged<float, kModeTruncate>(in, out, batch, D, k_per_row, out_offsets, s)
-                            : launch_ragged<double, kModeTruncate>(in, out, batch, D, k_per_row, out_offsets, s);
-  return dtype == ETN_F32 ? launch_ragged<float, kModeRenorm>(in, out, batch, D, k_per_row, out_offsets, s)
-                          : launch_ragged<double, kModeRenorm>(in, out, batch, D, k_per_row, out_offsets, s);
+    return finish(dtype == ETN_F32 ? launch_ragged<float, kModeTruncate>(in, out, batch, D, k_per_row, out_offsets, s)
+                                   : launch_ragged<double, kModeTruncate>(in, out, batch, D, k_per_row, out_offsets, s));
+  return finish(dtype == ETN_F32 ? launch_ragged<float, kModeRenorm>(in, out, batch, D, k_per_row, out_offsets, s)
+                                 : launch_ragged<double, kModeRenorm>(in, out, batch, D, k_per_row, out_offsets, s));
 }
 
 int etn_init(const int* device_ids, int n_devices) {
@@ -544,7 +561,9 @@ int embed_truncate_norm_host(int64_t batch, int64_t D, int64_t k, int dtype, int
     for (auto& t : th) t.join();
   }
   if (have_prev) cudaSetDevice(prev);
-  for (int rc : rcs) if (rc) return rc;
+  count(ETN_CTR_HOST_CALLS); count(ETN_CTR_HOST_ROWS, batch);
+  for (int rc : rcs) if (rc) return finish(rc);
+  count(ETN_CTR_H2D_BYTES, batch * kk * es); count(ETN_CTR_D2H_BYTES, batch * kk * es);
   return ETN_OK;
 }
 
@@ -598,6 +617,22 @@ int embed_truncate_norm_host_static(int64_t batch, int64_t D, int64_t k, int dty
   e = cudaStreamSynchronize(s);
   if (e != cudaSuccess && rc == 0) rc = (int)e;
   return rc;
+}
+
+int etn_get_counters(int64_t* out, int capacity) {
+  if (!out || capacity < 0) return ETN_ERR_NULL;
+  const int n = capacity < ETN_CTR_COUNT ? capacity : ETN_CTR_COUNT;
+  for (int i = 0; i < n; ++i) out[i] = g_ctr[i].load(std::memory_order_relaxed);
+  return n;
+}
+
+const char* etn_counter_name(int i) {
+  static const char* names[ETN_CTR_COUNT] = {
+      "llmcore_embed_gpu_device_calls_total", "llmcore_embed_gpu_device_rows_total",
+      "llmcore_embed_gpu_kernel_launches_total", "llmcore_embed_gpu_host_calls_total",
+      "llmcore_embed_gpu_host_rows_total", "llmcore_embed_gpu_h2d_bytes_total",
+      "llmcore_embed_gpu_d2h_bytes_total", "llmcore_embed_gpu_errors_total"};
+  return (i >= 0 && i < ETN_CTR_COUNT) ? names[i] : "";
 }
 
 int etn_fill_synthetic(uint64_t seed, int64_t row0, int64_t rows, int64_t D, int64_t ncols,

@@ -37,6 +37,7 @@ EXPORTS = (
     "etn_alloc_pinned", "etn_free_pinned", "embed_truncate_norm_host", "etn_fill_synthetic",
     "embed_truncate_norm_host_static",
     "etn_json_truncate_response", "etn_json_parse_array", "etn_json_format_array",
+    "etn_get_counters", "etn_counter_name",
 )
 
 
@@ -81,6 +82,9 @@ def lib() -> ctypes.CDLL:
         L.etn_json_parse_array.restype = i64
         L.etn_json_format_array.argtypes = [vp, i64, vp, ctypes.c_size_t]
         L.etn_json_format_array.restype = i64
+        L.etn_get_counters.argtypes = [vp, ci]
+        L.etn_counter_name.argtypes = [ci]
+        L.etn_counter_name.restype = ctypes.c_char_p
         _lib = L
     return _lib
 
@@ -296,3 +300,42 @@ def truncate_response_json(body: bytes, dims: int, renorm: bool | None = None, n
         code = int(n) if n > -1000 else int(-1000 - n)
         raise EtnError(code, strerror(code), "etn_json_truncate_response")
     return out.raw[:n], {"gpu_vectors": stats[0], "resliced_vectors": stats[1], "arrays": stats[2]}
+
+
+# ------------------------------------------------------------------- counters (N3) ----
+def counters() -> dict[str, int]:
+    """etn_get_counters as {metric name: value} — what the Go side would register beside the
+    embedding collectors of core/internal/metrics/metrics.go:9-26."""
+    buf = (ctypes.c_int64 * 32)()
+    n = lib().etn_get_counters(buf, 32)
+    return {lib().etn_counter_name(i).decode(): int(buf[i]) for i in range(n)}
+
+
+def metrics_text() -> str:
+    """Prometheus text exposition of the counters (the /metrics route, server.go:61)."""
+    return "".join(f"# TYPE {k} counter\n{k} {v}\n" for k, v in counters().items())
+
+
+# ------------------------------------------------------------ typed vectors (N2) ----
+def truncate_typed(embeddings, dims: int, renorm: bool | None = None) -> list:
+    """The op on the local Ollama branch: there the vectors arrive typed,
+    ``Embeddings [][]float64`` (handlers.go:1976-1984), and ``dimensions`` is ignored today
+    (handlers.go:1898-1939 never truncates).  Same rules as truncateEmbeddings: vectors with
+    len <= dims stay whole, longer ones keep their first ``dims`` components; dims <= 0 is a
+    no-op.  Typed rows pack with one copy, so every cut vector goes through the GPU host path
+    in one call per source length.  Returns a new list; the input is not modified."""
+    if renorm is None:
+        renorm = renorm_enabled()
+    out = [list(v) if not isinstance(v, list) else v for v in embeddings]
+    if dims <= 0:
+        return out
+    groups: dict[int, list[int]] = {}
+    for i, v in enumerate(out):
+        if len(v) > dims:
+            groups.setdefault(len(v), []).append(i)
+    for D, idx in groups.items():
+        x = np.array([out[i] for i in idx], dtype=np.float64)
+        y = truncate_norm_host(x, dims, TRUNCATE_RENORM if renorm else TRUNCATE)
+        for r, i in enumerate(idx):
+            out[i] = y[r].tolist()
+    return out

@@ -150,3 +150,47 @@ func allFloat64(emb []any) bool {
 	}
 	return true
 }
+
+// TruncateTyped is the op for the local Ollama branch (SURVEY.md §8(f) N2), where vectors
+// arrive typed: Embeddings [][]float64 (handlers.go:1976-1984) and `dimensions` is ignored
+// today.  Same rules as TruncateEmbeddings; without EMBED_RENORMALIZE it is a reslice.
+func TruncateTyped(embs [][]float64, dims int) {
+	if dims <= 0 {
+		return
+	}
+	renorm := ready && RenormEnabled()
+	for i, e := range embs {
+		if len(e) <= dims {
+			continue
+		}
+		if !renorm {
+			embs[i] = e[:dims]
+			continue
+		}
+		p := pool.Get().(*pinned)
+		if !p.ensure(len(e), dims) {
+			pool.Put(p)
+			embs[i] = e[:dims]
+			continue
+		}
+		copy(unsafe.Slice((*float64)(p.in), len(e)), e)
+		if rc := C.embed_truncate_norm_host(1, C.int64_t(len(e)), C.int64_t(dims), C.ETN_F64, C.ETN_TRUNCATE_RENORM,
+			p.in, 0, p.out, 0); rc == 0 {
+			copy(e[:dims], unsafe.Slice((*float64)(p.out), dims))
+		}
+		embs[i] = e[:dims]
+		pool.Put(p)
+	}
+}
+
+// Counters returns the library's cumulative counters keyed by Prometheus metric name
+// (SURVEY.md §8(f) N3); register them as CounterFuncs next to metrics.go:9-26.
+func Counters() map[string]int64 {
+	var buf [C.ETN_CTR_COUNT]C.int64_t
+	n := int(C.etn_get_counters(&buf[0], C.ETN_CTR_COUNT))
+	out := make(map[string]int64, n)
+	for i := 0; i < n; i++ {
+		out[C.GoString(C.etn_counter_name(C.int(i)))] = int64(buf[i])
+	}
+	return out
+}

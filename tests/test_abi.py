@@ -32,7 +32,7 @@ def test_header_cites_the_reference_per_entry_point():
     assert "handlers.go:2062-2078" in src and "handlers.go:1891-1893" in src
     for block in re.split(r"\n(?=/\*)", src):
         if "ETN_API" in block and "etn_free_pinned" not in block.split("ETN_API")[1][:40]:
-            assert re.search(r"(handlers|main|helpers)\.go:\d+|[Nn]o reference[\s\*]+counterpart|no[\s\*]+counterpart in the reference", block), block[:200]
+            assert re.search(r"(handlers|main|helpers|metrics|router|server)\.go:\d+|[Nn]o reference[\s\*]+counterpart|no[\s\*]+counterpart in the reference", block), block[:200]
 
 
 def test_version_and_strerror():
@@ -86,3 +86,15 @@ def test_host_mirror_config_surface():
     assert eg.truncate_embeddings(r, 2)["gpu_vectors"] == 0 and r["data"][0]["embedding"] == [1.0, 2.0]
     assert eg.truncate_embeddings({"data": 3}, 2)["gpu_vectors"] == 0
     assert eg.truncate_embeddings(r, 0)["gpu_vectors"] == 0 and eg.truncate_embeddings(r, -5)["gpu_vectors"] == 0
+
+
+def test_counters_and_typed_mirror_need_no_device():
+    c0 = eg.counters()
+    assert list(c0) == [eg.lib().etn_counter_name(i).decode() for i in range(8)] and all(k.startswith("llmcore_embed_gpu_") for k in c0)
+    eg.lib().embed_truncate_norm(2, 8, 0, eg.F64, None, None, None)          # shape error: counted nowhere but...
+    p = (ctypes.c_double * 4)()
+    assert eg.lib().embed_truncate_norm_host(2, 8, 4, eg.F64, 1, ctypes.addressof(p), 0, ctypes.addressof(p), 0) == eg.ERR_NOT_INIT
+    assert "# TYPE llmcore_embed_gpu_errors_total counter" in eg.metrics_text()
+    # N2 mirror: nothing to cut -> no device needed, input returned as is
+    assert eg.truncate_typed([[1.0, 2.0], [3.0]], 2) == [[1.0, 2.0], [3.0]]
+    assert eg.truncate_typed([[1.0, 2.0, 3.0]], 0) == [[1.0, 2.0, 3.0]]

@@ -159,3 +159,27 @@ def test_json_packer_renorm_against_reference(oracle):
     m = re.search(rb'"index": 0, "embedding": \[([^\]]*)\]|"embedding": \[([^\]]*)\], "index": 0', out)
     toks = (m.group(1) or m.group(2)).decode().split(",")
     assert len(toks) == 1024 and all(t == oracle.go_format_float(float(t)) for t in toks)
+
+
+# ------------------------------------------------------ typed vectors (N2), counters (N3) ----
+def test_typed_vectors_ollama_branch(oracle):
+    """handlers.go:1976-1984: Embeddings [][]float64; same cutting rules as truncateEmbeddings."""
+    x = oracle.fill(12, 9, 768, np.float64)
+    embs = [r.tolist() for r in x]
+    embs[2] = embs[2][:100]
+    embs[4] = embs[4][:300]
+    before = eg.counters()
+    got = eg.truncate_typed(embs, 256, renorm=False)
+    assert [len(v) for v in got] == [256, 256, 100, 256, 256, 256, 256, 256, 256]
+    assert all(g == e[:256] for g, e in zip(got, embs))
+    got = eg.truncate_typed(embs, 256, renorm=True)
+    for g, e in zip(got, embs):
+        if len(e) > 256:
+            _ulp(oracle, np.array(g), oracle.renorm_exact(np.array([e]), 256)[0])
+        else:
+            assert g == e
+    after = eg.counters()
+    d = {k: after[k] - before[k] for k in after}
+    assert d["llmcore_embed_gpu_host_calls_total"] == 4 and d["llmcore_embed_gpu_host_rows_total"] == 16
+    assert d["llmcore_embed_gpu_h2d_bytes_total"] == 16 * 256 * 8 == d["llmcore_embed_gpu_d2h_bytes_total"]
+    assert d["llmcore_embed_gpu_kernel_launches_total"] == 2 and d["llmcore_embed_gpu_errors_total"] == 0
