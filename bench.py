@@ -211,6 +211,42 @@ def quick_measure(torch, eg, wl, peak, steps=100, warmup=5):
             "frac_of_measured_peak": gbs / peak, "buffer_sets": n_sets, "steps": steps}
 
 
+def ragged_measure(torch, eg, peak, rows=1048576, D=4096, steps=50):
+    """C5: ragged mixed-request batch, float64, per-request k in {64,...,1024} (seed 5), one GPU's share
+    at bench scale.  Algorithmic bytes = sum over rows of 2 * k * 8."""
+    rng = np.random.default_rng(5)
+    parts, n = [], 0
+    while n < rows:
+        m = min(int(rng.integers(1, 2049)), rows - n)
+        parts.append(np.full(m, rng.choice([64, 128, 256, 512, 1024]), dtype=np.int32))
+        n += m
+    kpr = np.concatenate(parts)
+    off = np.zeros(rows + 1, dtype=np.int64)
+    np.cumsum(kpr, out=off[1:])
+    L = eg.lib()
+    st = torch.cuda.current_stream().cuda_stream
+    x = torch.empty((rows, D), dtype=torch.float64, device="cuda")
+    eg.check(L.etn_fill_synthetic(5, 0, rows, D, D, D, eg.F64, x.data_ptr(), st), "fill")
+    dk, do = torch.from_numpy(kpr).cuda(), torch.from_numpy(off[:-1].copy()).cuda()
+    out = torch.empty(int(off[-1]), dtype=torch.float64, device="cuda")
+    call = lambda: eg.check(L.embed_truncate_norm_ragged(rows, D, dk.data_ptr(), do.data_ptr(), eg.F64, eg.TRUNCATE_RENORM,
+                                                          x.data_ptr(), out.data_ptr(), st), "ragged")
+    for _ in range(5):
+        call()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        call()
+    e1.record()
+    torch.cuda.synchronize()
+    t = e0.elapsed_time(e1) * 1e-3 / steps
+    gbs = 2 * 8 * int(off[-1]) / t / 1e9
+    return {"workload": "ragged mixed-request batch, %d rows x %d float64, per-request k in {64,128,256,512,1024}, mean k %.1f" % (rows, D, kpr.mean()),
+            "vectors_per_s": rows / t, "us_per_launch": t * 1e6, "achieved_GBps": gbs, "frac_of_measured_peak": gbs / peak,
+            "kernel": "etn::rows_ring_kernel<double> (page-granular bulk-async ring)", "steps": steps}
+
+
 def run_ours(args, wl, rank, local_rank, world):
     import torch
     import torch.distributed as dist
@@ -329,6 +365,11 @@ def run_ours(args, wl, rank, local_rank, world):
             except Exception as e:  # noqa: BLE001
                 others[name] = {"error": repr(e)[:200]}
             torch.cuda.empty_cache()
+        try:
+            others["c5"] = ragged_measure(torch, eg, peak)
+        except Exception as e:  # noqa: BLE001
+            others["c5"] = {"error": repr(e)[:200]}
+        torch.cuda.empty_cache()
     avg_launch_s = ms_total * 1e-3 / args.steps
     algo_bytes = rows * 2 * k * es                          # per launch, per GPU
     achieved = algo_bytes / avg_launch_s / 1e9
