@@ -57,6 +57,7 @@ extern "C" {
 
 #define ETN_TRUNCATE 0
 #define ETN_TRUNCATE_RENORM 1
+#define ETN_JSON_BASE64 0x10 /* etn_json_truncate_response only: cut base64 float32 embeddings too */
 
 #define ETN_OK 0
 #define ETN_ERR_NULL (-1)     /* a required pointer is NULL */
@@ -179,7 +180,12 @@ ETN_API int embed_truncate_norm_host_static(int64_t batch, int64_t D, int64_t k,
  * (handlers.go:1891).  Returns the number of bytes written to `out`, or a negative code:
  * ETN_ERR_SHAPE = out_cap too small (len + 2 always suffices for TRUNCATE; allow 26 bytes per
  * kept number for RENORM), ETN_ERR_JSON / ETN_ERR_JSON_DUP = fall back to the reference path,
- * -1000 - c = CUDA error c.  stats (may be NULL) receives {vectors renormalised on the GPU,
+ * -1000 - c = CUDA error c.  mode | ETN_JSON_BASE64 also treats an
+ * "embedding" that is a base64 string of little-endian float32 (OpenAI's
+ * encoding_format "base64", parsed at handlers.go:1831 but never forwarded) as a vector:
+ * its bytes go into pinned memory without any number parsing and come back re-encoded.  The
+ * reference leaves such strings untouched (handlers.go:2073), hence the opt-in flag.
+ * stats (may be NULL) receives {vectors renormalised on the GPU,
  * vectors cut as text, embedding arrays seen}. */
 ETN_API int64_t etn_json_truncate_response(const char *json, size_t len, int64_t dims, int mode,
                                            char *out, size_t out_cap, int n_devices,

@@ -134,7 +134,53 @@ struct Span {
   int64_t count;       // elements
   int64_t cut;         // offset one past the `dims`-th element (valid when count > dims)
   bool numeric;        // the first min(count, dims) elements are all JSON numbers
+  bool b64 = false;    // a base64 string of little-endian float32 (open/close = the quotes)
 };
+
+// ---- base64 (RFC 4648, standard alphabet, '=' padding): OpenAI's encoding_format "base64"
+// carries each vector as little-endian float32 bytes.
+const char kB64[] = "ABCDEFGHIJKLMNOPQRSTUVWXYZabcdefghijklmnopqrstuvwxyz0123456789+/";
+struct B64Table {
+  signed char v[256];
+  B64Table() { memset(v, -1, sizeof v); for (int i = 0; i < 64; ++i) v[(unsigned char)kB64[i]] = (signed char)i; }
+};
+const B64Table kB64Dec;
+
+// Decoded byte count of a padded base64 text, or -1 if it is not one.
+int64_t b64_decoded_len(const char* t, size_t n) {
+  if (n == 0 || n % 4 != 0) return n == 0 ? 0 : -1;
+  size_t pad = 0;
+  if (t[n - 1] == '=') { ++pad; if (t[n - 2] == '=') ++pad; }
+  for (size_t i = 0; i < n - pad; ++i) if (kB64Dec.v[(unsigned char)t[i]] < 0) return -1;
+  return (int64_t)(n / 4 * 3 - pad);
+}
+// Decodes the first nbytes bytes (nbytes <= decoded length).
+void b64_decode_prefix(const char* t, size_t nbytes, unsigned char* dst) {
+  size_t o = 0;
+  for (size_t i = 0; o < nbytes; i += 4) {
+    const unsigned a = (unsigned)kB64Dec.v[(unsigned char)t[i]], b = (unsigned)kB64Dec.v[(unsigned char)t[i + 1]];
+    const unsigned c = t[i + 2] == '=' ? 0u : (unsigned)kB64Dec.v[(unsigned char)t[i + 2]];
+    const unsigned d = t[i + 3] == '=' ? 0u : (unsigned)kB64Dec.v[(unsigned char)t[i + 3]];
+    const unsigned w = (a << 18) | (b << 12) | (c << 6) | d;
+    dst[o++] = (unsigned char)(w >> 16);
+    if (o < nbytes) dst[o++] = (unsigned char)(w >> 8);
+    if (o < nbytes) dst[o++] = (unsigned char)w;
+  }
+}
+size_t b64_encoded_len(size_t nbytes) { return (nbytes + 2) / 3 * 4; }
+void b64_encode(const unsigned char* src, size_t nbytes, char* dst) {
+  size_t i = 0, o = 0;
+  for (; i + 3 <= nbytes; i += 3) {
+    const unsigned w = ((unsigned)src[i] << 16) | ((unsigned)src[i + 1] << 8) | src[i + 2];
+    dst[o++] = kB64[w >> 18]; dst[o++] = kB64[(w >> 12) & 63]; dst[o++] = kB64[(w >> 6) & 63]; dst[o++] = kB64[w & 63];
+  }
+  if (i < nbytes) {
+    const unsigned w = ((unsigned)src[i] << 16) | (i + 1 < nbytes ? (unsigned)src[i + 1] << 8 : 0u);
+    dst[o++] = kB64[w >> 18]; dst[o++] = kB64[(w >> 12) & 63];
+    dst[o++] = i + 1 < nbytes ? kB64[(w >> 6) & 63] : '=';
+    dst[o++] = '=';
+  }
+}
 
 // p at '[' of an embedding array.  Records the span; `dims` bounds the numeric check.
 bool scan_embedding(Scanner& sc, int64_t dims, Span* out) {
@@ -165,7 +211,7 @@ bool scan_embedding(Scanner& sc, int64_t dims, Span* out) {
 // Returns 0, ETN_ERR_JSON for malformed input, ETN_ERR_JSON_DUP when "data" or an item's
 // "embedding" occurs twice (Go keeps the last one and drops the other on re-encode; a splice
 // cannot mimic that, the caller should take the reference path).
-int find_embeddings(const char* json, size_t len, int64_t dims, std::vector<Span>* spans) {
+int find_embeddings(const char* json, size_t len, int64_t dims, bool b64, std::vector<Span>* spans) {
   Scanner sc{json, json + len, json};
   sc.ws();
   if (sc.p >= sc.e || *sc.p != '{') {            // not an object: Go's Decode(&map) would fail earlier
@@ -204,6 +250,16 @@ int find_embeddings(const char* json, size_t len, int64_t dims, std::vector<Span
               Span s;
               if (!scan_embedding(sc, dims, &s)) return ETN_ERR_JSON;
               spans->push_back(s);
+            } else if (is_emb && b64 && sc.p < sc.e && *sc.p == '"') {
+              Span s;
+              s.open = sc.p - sc.b;
+              if (!sc.skip_string()) return ETN_ERR_JSON;
+              s.close = sc.p - sc.b;
+              const int64_t nb = b64_decoded_len(json + s.open + 1, (size_t)(s.close - s.open - 2));
+              if (nb > 0 && nb % 4 == 0) {          // float32 vector; anything else stays untouched
+                s.count = nb / 4; s.cut = -1; s.numeric = true; s.b64 = true;
+                spans->push_back(s);
+              }
             } else if (!sc.skip_value(2)) return ETN_ERR_JSON;
             sc.ws();
             if (sc.p < sc.e && *sc.p == ',') { ++sc.p; continue; }
@@ -323,24 +379,28 @@ int64_t etn_json_parse_array(const char* text, size_t len, double* dst, int64_t 
 
 int64_t etn_json_truncate_response(const char* json, size_t len, int64_t dims, int mode, char* out,
                                    size_t out_cap, int n_devices, int64_t* stats) {
+  const bool b64 = (mode & ETN_JSON_BASE64) != 0;
+  mode &= ~ETN_JSON_BASE64;
   if (mode != ETN_TRUNCATE && mode != ETN_TRUNCATE_RENORM) return ETN_ERR_ENUM;
   if (!json || !out) return ETN_ERR_NULL;
   if (stats) { stats[0] = stats[1] = stats[2] = 0; }
   std::vector<Span> spans;
   if (dims > 0) {
-    const int rc = find_embeddings(json, len, dims, &spans);
+    const int rc = find_embeddings(json, len, dims, b64, &spans);
     if (rc != ETN_OK) return rc;
   }
   // vectors that go through the GPU: longer than dims, numeric prefix, renorm requested
-  std::vector<size_t> gpu;
+  std::vector<size_t> gpu64, gpu32;
   if (mode == ETN_TRUNCATE_RENORM)
     for (size_t i = 0; i < spans.size(); ++i)
-      if (spans[i].count > dims && spans[i].numeric) gpu.push_back(i);
+      if (spans[i].count > dims && spans[i].numeric) (spans[i].b64 ? gpu32 : gpu64).push_back(i);
   double* vals = nullptr;
+  float* vals32 = nullptr;
   void* own = nullptr;
   std::unique_lock<std::mutex> pin_lock(g_pin.mu, std::defer_lock);
-  if (!gpu.empty()) {
-    const size_t need = gpu.size() * (size_t)dims * sizeof(double);
+  if (!gpu64.empty() || !gpu32.empty()) {
+    const size_t need64 = gpu64.size() * (size_t)dims * sizeof(double);
+    const size_t need = need64 + gpu32.size() * (size_t)dims * sizeof(float);
     if (pin_lock.try_lock()) {
       if (g_pin.cap < need) {
         etn_free_pinned(g_pin.in);
@@ -351,19 +411,25 @@ int64_t etn_json_truncate_response(const char* json, size_t len, int64_t dims, i
       if (!vals) pin_lock.unlock();
     }
     if (!vals) { own = etn_alloc_pinned(need); vals = (double*)own; }
-    if (!vals) return 2;                           // cudaErrorMemoryAllocation
-    for (size_t g = 0; g < gpu.size(); ++g) {
-      const Span& s = spans[gpu[g]];
+    if (!vals) return -1000 - 2;                   // cudaErrorMemoryAllocation
+    vals32 = (float*)((char*)vals + need64);
+    for (size_t g = 0; g < gpu64.size(); ++g) {
+      const Span& s = spans[gpu64[g]];
       const int64_t n = etn_json_parse_array(json + s.open, (size_t)(s.close - s.open), vals + g * dims, dims);
       if (n < 0) { if (own) etn_free_pinned(own); return n; }
     }
-    // prefix-only buffer: D == k == dims, renormalised in place through the host path
-    const int rc = embed_truncate_norm_host((int64_t)gpu.size(), dims, dims, ETN_F64, ETN_TRUNCATE_RENORM, vals, 0,
-                                            vals, n_devices);
+    for (size_t g = 0; g < gpu32.size(); ++g)      // zero-parse path: bytes straight into pinned float32
+      b64_decode_prefix(json + spans[gpu32[g]].open + 1, (size_t)dims * 4, (unsigned char*)(vals32 + g * dims));
+    // prefix-only buffers: D == k == dims, renormalised in place through the host path
+    int rc = 0;
+    if (!gpu64.empty())
+      rc = embed_truncate_norm_host((int64_t)gpu64.size(), dims, dims, ETN_F64, ETN_TRUNCATE_RENORM, vals, 0, vals, n_devices);
+    if (rc == 0 && !gpu32.empty())
+      rc = embed_truncate_norm_host((int64_t)gpu32.size(), dims, dims, ETN_F32, ETN_TRUNCATE_RENORM, vals32, 0, vals32, n_devices);
     if (rc != 0) { if (own) etn_free_pinned(own); return rc < 0 ? rc : -1000 - rc; }
   }
   // splice
-  size_t o = 0, src = 0, g = 0;
+  size_t o = 0, src = 0, g64 = 0, g32 = 0;
   auto put = [&](const char* p, size_t n) -> bool {
     if (o + n > out_cap) return false;
     memcpy(out + o, p, n);
@@ -371,16 +437,35 @@ int64_t etn_json_truncate_response(const char* json, size_t len, int64_t dims, i
     return true;
   };
   bool fits = true;
+  std::vector<unsigned char> tmp;
   for (size_t i = 0; i < spans.size() && fits; ++i) {
     const Span& s = spans[i];
     if (s.count <= dims) continue;                 // left whole, never padded (handlers.go:2074)
     fits = put(json + src, (size_t)s.open - src);
     if (!fits) break;
-    if (g < gpu.size() && gpu[g] == i) {
-      const int64_t w = etn_json_format_array(vals + g * dims, dims, out + o, out_cap - o);
+    if (s.b64) {
+      const size_t nbytes = (size_t)dims * 4, enc = b64_encoded_len(nbytes);
+      if (o + enc + 2 > out_cap) { fits = false; break; }
+      const unsigned char* bytes;
+      if (g32 < gpu32.size() && gpu32[g32] == i) {
+        bytes = (const unsigned char*)(vals32 + g32 * dims);
+        ++g32;
+        if (stats) ++stats[0];
+      } else {
+        tmp.resize(nbytes);
+        b64_decode_prefix(json + s.open + 1, nbytes, tmp.data());
+        bytes = tmp.data();
+        if (stats) ++stats[1];
+      }
+      out[o++] = '"';
+      b64_encode(bytes, nbytes, out + o);
+      o += enc;
+      out[o++] = '"';
+    } else if (g64 < gpu64.size() && gpu64[g64] == i) {
+      const int64_t w = etn_json_format_array(vals + g64 * dims, dims, out + o, out_cap - o);
       if (w < 0) { fits = w != ETN_ERR_SHAPE; if (fits) { if (own) etn_free_pinned(own); return w; } break; }
       o += (size_t)w;
-      ++g;
+      ++g64;
       if (stats) ++stats[0];
     } else {                                       // the reference reslice, on the text: tokens kept verbatim
       fits = put(json + s.open, (size_t)(s.cut - s.open)) && put("]", 1);

@@ -283,7 +283,10 @@ def shard_ragged(k_per_row, D: int, world: int) -> list[tuple[int, int]]:
 
 
 # ------------------------------------------------------------------ JSON packer (N1) ----
-def truncate_response_json(body: bytes, dims: int, renorm: bool | None = None, n_devices: int = 0):
+JSON_BASE64 = 0x10
+
+
+def truncate_response_json(body: bytes, dims: int, renorm: bool | None = None, n_devices: int = 0, base64_vectors: bool = False):
     """etn_json_truncate_response: the provider's response text in, the handler's response
     text out, with the embedding arrays cut (and, with renorm, renormalised on the GPU)
     without ever building the decoded map (handlers.go:2047-2050 / helpers.go:11-15).
@@ -291,7 +294,7 @@ def truncate_response_json(body: bytes, dims: int, renorm: bool | None = None, n
     should take the reference path instead."""
     if renorm is None:
         renorm = renorm_enabled()
-    mode = TRUNCATE_RENORM if renorm else TRUNCATE
+    mode = (TRUNCATE_RENORM if renorm else TRUNCATE) | (JSON_BASE64 if base64_vectors else 0)
     cap = len(body) + 2 if not renorm else len(body) + 2 + 26 * max(dims, 0) * (body.count(b'"embedding"') + 1)
     out = ctypes.create_string_buffer(cap)
     stats = (ctypes.c_int64 * 3)()

@@ -258,3 +258,21 @@ def response_ref(body: bytes, dims: int, renorm: bool):
                     v = np.array([[float(t) for t in it["embedding"]]], dtype=np.float64)
                     it["embedding"] = renorm_exact(v, dims)[0].tolist()
     return result
+
+
+def b64_vector_ref(text: str, dims: int, renorm: bool):
+    """OpenAI encoding_format "base64": the string carries little-endian float32 (N4).  Returns
+    the string the packer must produce with ETN_JSON_BASE64: cut to dims floats when longer,
+    exactly renormalised when asked, untouched when it is not a float32 vector or not longer."""
+    import base64
+    import binascii
+    try:
+        raw = base64.b64decode(text, validate=True)
+    except (binascii.Error, ValueError):
+        return text
+    if len(raw) == 0 or len(raw) % 4 != 0 or dims <= 0 or len(raw) // 4 <= dims:
+        return text
+    v = np.frombuffer(raw, dtype="<f4")[:dims].astype(np.float32)
+    if renorm:
+        v = renorm_exact(v[None, :], dims)[0]
+    return base64.b64encode(v.astype("<f4").tobytes()).decode()

@@ -183,3 +183,22 @@ def test_typed_vectors_ollama_branch(oracle):
     assert d["llmcore_embed_gpu_host_calls_total"] == 4 and d["llmcore_embed_gpu_host_rows_total"] == 16
     assert d["llmcore_embed_gpu_h2d_bytes_total"] == 16 * 256 * 8 == d["llmcore_embed_gpu_d2h_bytes_total"]
     assert d["llmcore_embed_gpu_kernel_launches_total"] == 2 and d["llmcore_embed_gpu_errors_total"] == 0
+
+
+def test_json_packer_base64_renorm(oracle):
+    """N4: base64 float32 vectors reach the GPU without any number parsing."""
+    import base64
+    x = oracle.fill(3, 40, 4096, np.float32)
+    items = [{"index": i, "embedding": base64.b64encode(r.astype("<f4").tobytes()).decode()} for i, r in enumerate(x)]
+    items[3]["embedding"] = base64.b64encode(x[3, :100].tobytes()).decode()      # shorter than dims
+    items.append({"index": 40, "embedding": oracle.fill(3, 1, 4096, np.float64)[0].tolist()})   # arrays still work
+    body = json.dumps({"data": items}).encode()
+    out, stats = eg.truncate_response_json(body, 1024, renorm=True, base64_vectors=True)
+    got = json.loads(out)["data"]
+    assert stats["gpu_vectors"] == 40 and stats["arrays"] == 42
+    for g, it in zip(got[:40], items[:40]):
+        want = oracle.b64_vector_ref(it["embedding"], 1024, True)
+        a = np.frombuffer(base64.b64decode(g["embedding"]), dtype="<f4")
+        b = np.frombuffer(base64.b64decode(want), dtype="<f4")
+        _ulp(oracle, a.copy(), b.copy())
+    _ulp(oracle, np.array(got[40]["embedding"]), oracle.renorm_exact(np.array([items[40]["embedding"]]), 1024)[0])

@@ -125,3 +125,29 @@ def test_c1_sized_response_truncate(oracle):
     got = json.loads(out)
     assert [len(d["embedding"]) for d in got["data"]] == [1024] * 64 and stats["resliced_vectors"] == 64
     assert np.array_equal(np.array([d["embedding"] for d in got["data"]]), x[:, :1024])
+
+
+def _b64(v):
+    import base64
+    return base64.b64encode(np.asarray(v, dtype="<f4").tobytes()).decode()
+
+
+def test_base64_vectors_truncate(oracle):
+    """N4: with ETN_JSON_BASE64 a base64 float32 embedding is cut like an array; without the
+    flag it is left alone, as the reference does (handlers.go:2073)."""
+    rng = np.random.default_rng(4)
+    vs = [rng.standard_normal(n).astype(np.float32) for n in (40, 16, 17, 3, 41)]
+    items = [{"object": "embedding", "index": i, "embedding": _b64(v)} for i, v in enumerate(vs)]
+    items += [{"embedding": "not base64!"}, {"embedding": "QUJD"}, {"embedding": ""}, {"embedding": [1.0, 2.0, 3.0]}]
+    body = json.dumps({"data": items, "model": "m"}).encode()
+    assert eg.truncate_response_json(body, 16, renorm=False)[0].count(b'"embedding":') == 9
+    untouched, _ = eg.truncate_response_json(body, 16, renorm=False)
+    assert json.loads(untouched)["data"][0]["embedding"] == items[0]["embedding"]           # flag off: reference behaviour
+    for dims in (16, 1, 2, 5):
+        out, stats = eg.truncate_response_json(body, dims, renorm=False, base64_vectors=True)
+        got = json.loads(out)["data"]
+        for g, it in zip(got, items):
+            if isinstance(it["embedding"], str):
+                assert g["embedding"] == oracle.b64_vector_ref(it["embedding"], dims, False), dims
+        assert got[8]["embedding"] == [1.0, 2.0, 3.0][:dims]
+        assert stats["gpu_vectors"] == 0
