@@ -19,11 +19,14 @@
 // then 'e' form with "e-0d" shortened to "e-d".
 #include "../../include/embed_truncate_norm.h"
 
+#include <algorithm>
+#include <atomic>
 #include <charconv>
 #include <cmath>
 #include <cstring>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 namespace {
@@ -324,6 +327,18 @@ size_t format_go_float(double f, char* out) {
   return (size_t)(o - out);
 }
 
+// Vectors are independent, so number parsing and formatting spread over host threads
+// (handlers run one goroutine per connection; a large response still deserves the cores).
+template <typename F>
+void parallel_for(size_t n, size_t grain, F f) {
+  size_t nt = std::min<size_t>(std::min<size_t>(std::thread::hardware_concurrency(), 16), n / grain);
+  if (nt <= 1) { for (size_t i = 0; i < n; ++i) f(i); return; }
+  std::vector<std::thread> th;
+  for (size_t t = 0; t < nt; ++t)
+    th.emplace_back([=] { for (size_t i = t; i < n; i += nt) f(i); });
+  for (auto& x : th) x.join();
+}
+
 // Reusable pinned staging for the rewrite (one per thread would be better still; handlers
 // call concurrently, so a mutex guards the shared one and overflow callers allocate their own).
 struct PinPool {
@@ -413,13 +428,16 @@ int64_t etn_json_truncate_response(const char* json, size_t len, int64_t dims, i
     if (!vals) { own = etn_alloc_pinned(need); vals = (double*)own; }
     if (!vals) return -1000 - 2;                   // cudaErrorMemoryAllocation
     vals32 = (float*)((char*)vals + need64);
-    for (size_t g = 0; g < gpu64.size(); ++g) {
+    std::atomic<int64_t> parse_err{0};
+    parallel_for(gpu64.size(), 8, [&](size_t g) {
       const Span& s = spans[gpu64[g]];
       const int64_t n = etn_json_parse_array(json + s.open, (size_t)(s.close - s.open), vals + g * dims, dims);
-      if (n < 0) { if (own) etn_free_pinned(own); return n; }
-    }
-    for (size_t g = 0; g < gpu32.size(); ++g)      // zero-parse path: bytes straight into pinned float32
+      if (n < 0) parse_err.store(n);
+    });
+    if (parse_err.load() < 0) { if (own) etn_free_pinned(own); return parse_err.load(); }
+    parallel_for(gpu32.size(), 64, [&](size_t g) {  // zero-parse path: bytes straight into pinned float32
       b64_decode_prefix(json + spans[gpu32[g]].open + 1, (size_t)dims * 4, (unsigned char*)(vals32 + g * dims));
+    });
     // prefix-only buffers: D == k == dims, renormalised in place through the host path
     int rc = 0;
     if (!gpu64.empty())
@@ -428,6 +446,13 @@ int64_t etn_json_truncate_response(const char* json, size_t len, int64_t dims, i
       rc = embed_truncate_norm_host((int64_t)gpu32.size(), dims, dims, ETN_F32, ETN_TRUNCATE_RENORM, vals32, 0, vals32, n_devices);
     if (rc != 0) { if (own) etn_free_pinned(own); return rc < 0 ? rc : -1000 - rc; }
   }
+  // format the renormalised float64 vectors on all cores, then splice sequentially
+  const size_t fstride = (size_t)dims * 34 + 2;
+  std::vector<char> ftext(gpu64.size() * fstride);
+  std::vector<int64_t> flen(gpu64.size());
+  parallel_for(gpu64.size(), 8, [&](size_t g) {
+    flen[g] = etn_json_format_array(vals + g * dims, dims, ftext.data() + g * fstride, fstride);
+  });
   // splice
   size_t o = 0, src = 0, g64 = 0, g32 = 0;
   auto put = [&](const char* p, size_t n) -> bool {
@@ -462,9 +487,10 @@ int64_t etn_json_truncate_response(const char* json, size_t len, int64_t dims, i
       o += enc;
       out[o++] = '"';
     } else if (g64 < gpu64.size() && gpu64[g64] == i) {
-      const int64_t w = etn_json_format_array(vals + g64 * dims, dims, out + o, out_cap - o);
-      if (w < 0) { fits = w != ETN_ERR_SHAPE; if (fits) { if (own) etn_free_pinned(own); return w; } break; }
-      o += (size_t)w;
+      const int64_t w = flen[g64];
+      if (w < 0) { if (own) etn_free_pinned(own); return w; }     // NaN/Inf: Go's encoder would refuse too
+      fits = put(ftext.data() + g64 * fstride, (size_t)w);
+      if (!fits) break;
       ++g64;
       if (stats) ++stats[0];
     } else {                                       // the reference reslice, on the text: tokens kept verbatim

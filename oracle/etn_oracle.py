@@ -248,8 +248,9 @@ def response_ref(body: bytes, dims: int, renorm: bool):
     import json
     result = json.loads(body)
     if dims > 0:
-        before = {id(it): len(it["embedding"]) for it in result.get("data", []) if isinstance(result.get("data"), list)
-                  and isinstance(it, dict) and isinstance(it.get("embedding"), list)} if isinstance(result, dict) else {}
+        data = result.get("data") if isinstance(result, dict) else None
+        before = {id(it): len(it["embedding"]) for it in (data if isinstance(data, list) else [])
+                  if isinstance(it, dict) and isinstance(it.get("embedding"), list)}
         truncate_embeddings_ref(result, dims)
         if renorm and isinstance(result, dict) and isinstance(result.get("data"), list):
             for it in result["data"]:

@@ -151,3 +151,54 @@ def test_base64_vectors_truncate(oracle):
                 assert g["embedding"] == oracle.b64_vector_ref(it["embedding"], dims, False), dims
         assert got[8]["embedding"] == [1.0, 2.0, 3.0][:dims]
         assert stats["gpu_vectors"] == 0
+
+
+def test_fuzz_random_json_matches_reference(oracle):
+    """Random JSON documents shaped like (and unlike) provider responses: the rewrite must
+    equal decode -> truncateEmbeddings -> encode as a JSON value, for every dims."""
+    rng = np.random.default_rng(77)
+
+    def rnd_scalar():
+        c = rng.integers(0, 7)
+        if c == 0: return None
+        if c == 1: return bool(rng.integers(0, 2))
+        if c == 2: return int(rng.integers(-10**9, 10**9))
+        if c == 3: return float(rng.standard_normal() * 10.0 ** rng.integers(-12, 12))
+        if c == 4: return "".join(rng.choice(list('ab]["\\\\{},: é\n'), size=rng.integers(0, 8)))
+        if c == 5: return float(rng.integers(-5, 5))
+        return 1e-7 * float(rng.integers(1, 100))
+
+    def rnd_value(depth):
+        c = rng.integers(0, 10)
+        if depth > 3 or c < 5: return rnd_scalar()
+        if c < 8: return [rnd_value(depth + 1) for _ in range(rng.integers(0, 5))]
+        return {rnd_key(): rnd_value(depth + 1) for _ in range(rng.integers(0, 4))}
+
+    def rnd_key():
+        return str(rng.choice(["data", "embedding", "index", "object", "x", "usage", "data ", "Embedding"]))
+
+    def rnd_embedding():
+        c = rng.integers(0, 8)
+        if c == 0: return rnd_value(2)
+        n = int(rng.integers(0, 12))
+        v = [float(rng.standard_normal()) for _ in range(n)]
+        if c == 1 and n: v[int(rng.integers(0, n))] = rnd_value(2)
+        return v
+
+    def rnd_item():
+        c = rng.integers(0, 8)
+        if c == 0: return rnd_value(1)
+        it = {"index": int(rng.integers(0, 99))}
+        if c != 1: it["embedding"] = rnd_embedding()
+        if c == 2: it["extra"] = rnd_value(1)
+        return it
+
+    for trial in range(400):
+        doc = {rnd_key() + str(i): rnd_value(1) for i in range(rng.integers(0, 3))}
+        c = rng.integers(0, 10)
+        if c < 8: doc["data"] = [rnd_item() for _ in range(rng.integers(0, 6))]
+        elif c == 8: doc["data"] = rnd_value(1)
+        body = json.dumps(doc, indent=int(rng.integers(0, 3)) or None, ensure_ascii=bool(rng.integers(0, 2))).encode()
+        for dims in (1, 3, 8):
+            out, _ = eg.truncate_response_json(body, dims, renorm=False)
+            assert json.loads(out) == oracle.response_ref(body, dims, renorm=False), (trial, dims, body)
