@@ -195,7 +195,7 @@ def test_json_packer_base64_renorm(oracle):
     body = json.dumps({"data": items}).encode()
     out, stats = eg.truncate_response_json(body, 1024, renorm=True, base64_vectors=True)
     got = json.loads(out)["data"]
-    assert stats["gpu_vectors"] == 40 and stats["arrays"] == 42
+    assert stats["gpu_vectors"] == 40 and stats["arrays"] == 41
     for g, it in zip(got[:40], items[:40]):
         want = oracle.b64_vector_ref(it["embedding"], 1024, True)
         a = np.frombuffer(base64.b64decode(g["embedding"]), dtype="<f4")
