@@ -144,7 +144,24 @@ def cpu_go_loop(wl, budget_s: float, sample_rows: int, steps: int | None = None,
         el = time.perf_counter() - t0
         if (steps is not None and n >= steps) or (steps is None and el >= budget_s):
             break
-    return {"value": sample_rows * n / el, "unit": "vectors/s", "cores": threads, "kind": "port",
+    variants = None
+    if steps is None:
+        # the same loop on one thread (one handler goroutine), and a vectorised
+        # C build as "best CPU" — reported next to the headline baseline, a few seconds each
+        variants = {}
+        for label, fn, nt in (("go_loop_1_thread", oracle.renorm_go, 1), ("vectorised_c_all_threads", oracle.renorm_fast, threads)):
+            try:
+                sub = x[: max(1, sample_rows // (8 if nt == 1 else 1))]
+                so = out[: len(sub)]
+                fn(sub, k, nthreads=nt, out=so)
+                m, t1 = 0, time.perf_counter()
+                while time.perf_counter() - t1 < 3.0:
+                    fn(sub, k, nthreads=nt, out=so)
+                    m += 1
+                variants[label] = {"value": len(sub) * m / (time.perf_counter() - t1), "unit": "vectors/s", "cores": nt}
+            except Exception as e:  # noqa: BLE001
+                variants[label] = {"error": repr(e)[:120]}
+    return {"value": sample_rows * n / el, "unit": "vectors/s", "cores": threads, "kind": "port", "variants": variants,
             "sample": f"{n} passes of oracle O-go (scalar float64 loop, no FMA, OpenMP over {threads} threads) on "
                       f"{sample_rows} x {k} {wl['dtype']} prefix rows of {wl['desc']}; {el:.1f} s",
             "seconds": el, "steps": n}
@@ -387,7 +404,7 @@ def run_ours(args, wl, rank, local_rank, world):
     cpu = None
     if world == 1 and not args.no_cpu:
         r = cpu_go_loop(wl, budget_s=12.0, sample_rows=min(rows, 131072))
-        cpu = {k_: r[k_] for k_ in ("value", "unit", "cores", "kind", "sample")}
+        cpu = {k_: r[k_] for k_ in ("value", "unit", "cores", "kind", "sample", "variants")}
     line = {
         "metric": "truncated+renormalised vectors/sec", "value": value, "unit": "vectors/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,

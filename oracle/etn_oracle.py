@@ -119,6 +119,26 @@ def renorm_go(x: np.ndarray, k: int, nthreads: int = 1, out: np.ndarray | None =
     return out
 
 
+_fast = None
+
+
+def renorm_fast(x: np.ndarray, k: int, nthreads: int = 1, out: np.ndarray | None = None) -> np.ndarray:
+    """Vectorised "best CPU" baseline (etn_oracle_fast.c); timing only, not the oracle of record."""
+    global _fast
+    if _fast is None:
+        so = os.path.join(_HERE, "libetn_oracle_fast.so")
+        if not os.path.exists(so):
+            subprocess.check_call(["make", "-C", _HERE, "-s", "libetn_oracle_fast.so"])
+        _fast = ctypes.CDLL(so)
+        _fast.etn_oracle_renorm_fast.argtypes = [ctypes.c_int64] * 3 + [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
+    x = np.ascontiguousarray(x)
+    batch, D = x.shape
+    if out is None:
+        out = np.empty((batch, min(k, D)), dtype=x.dtype)
+    _check(_fast.etn_oracle_renorm_fast(batch, D, k, dtype_code(x.dtype), _ptr(x), _ptr(out), nthreads), "renorm_fast")
+    return out
+
+
 def ragged_offsets(k_per_row: np.ndarray, D: int) -> np.ndarray:
     """Exclusive prefix sum of min(k, D): CSR element offsets, length batch+1."""
     kk = np.minimum(np.asarray(k_per_row, dtype=np.int64), D)
