@@ -41,6 +41,7 @@ struct DeviceInfo {
   std::atomic<int> sms{0};
 };
 constexpr int kMaxDevices = 64;
+constexpr int64_t kWideMaxRowBytes = 112 * 1024;    // two row buffers must fit the 227 KiB of shared memory
 DeviceInfo g_info[kMaxDevices];
 
 int sm_count(int dev, int* out) {
@@ -109,13 +110,41 @@ int launch_reg(const void* in, void* out, int64_t batch, int64_t in_pitch, int n
   return launch_kernel(kern, grid, s, (const char*)in, (char*)out, batch, in_pitch, nvec, D, k_per_row, out_offsets);
 }
 
-template <typename T, int VB, int NV, int G, int MODE, int MINB>
-int launch_coop(const void* in, void* out, int64_t batch, int64_t in_pitch, int nvec, cudaStream_t s) {
-  auto kern = rows_coop_kernel<T, VB, NV, G, MODE, MINB, VB == 32 ? 1 : 0>;
-  int grid = 0;
-  const int64_t rows_per_block = kWarpsPerBlock / G;
-  if (int rc = grid_for(kern, (batch + rows_per_block - 1) / rows_per_block, 0, &grid)) return rc;
-  return launch_kernel(kern, grid, s, (const char*)in, (char*)out, batch, in_pitch, nvec);
+// Wide rows: one row per block iteration, double-buffered in shared memory.
+template <typename T, int MODE>
+int launch_wide(const void* in, void* out, int64_t batch, int64_t in_pitch, int nvec16, cudaStream_t s) {
+  auto kern = rows_wide_kernel<T, MODE>;
+  const size_t stride = ((size_t)nvec16 * 16 + 127) & ~(size_t)127;
+  const size_t smem = 2 * stride;
+  int dev = 0, sms = 148;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  sm_count(dev, &sms);
+  {  // dynamic shared memory beyond 48 KiB is an opt-in per function and device; the largest size is set once
+    static std::atomic<uint64_t> done{0};
+    const uint64_t bit = 1ull << (dev & 63);
+    if (!(done.load(std::memory_order_acquire) & bit)) {
+      e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * (int)kWideMaxRowBytes);
+      if (e != cudaSuccess) return (int)e;
+      done.fetch_or(bit, std::memory_order_release);
+    }
+  }
+  // two rows per block keep one copy in flight behind the row being reduced; with a single
+  // resident block per SM (rows > 56 KiB) four amortise the pipeline fill better
+  int rpb = smem > 113 * 1024 ? 4 : 2;
+  rpb = (int)std::max<int64_t>(1, std::min<int64_t>(rpb, batch / ((int64_t)sms * 2)));
+  const int64_t blocks = std::min<int64_t>((batch + rpb - 1) / rpb, (int64_t)1 << 30);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)std::max<int64_t>(blocks, 1));
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return counted_launch(cudaLaunchKernelEx(&cfg, kern, (const char*)in, (char*)out, batch, in_pitch, nvec16, rpb));
 }
 
 // Bulk-async (TMA) ring kernel: 4 warps per block, each with its own S-slot ring of row
@@ -169,9 +198,11 @@ int launch_general(const void* in, void* out, int64_t batch, int64_t D, int64_t 
 }
 
 // Dense rows.  Kernel choice by prefix size and alignment:
-//   32-byte tileable: rows_reg (<= 8 KiB per row), rows_coop with 2/4/8 warps per row (<= 64 KiB)
-//   16-byte tileable: rows_reg with 128-bit accesses (<= 8 KiB)
-//   anything else:    rows_general
+//   16-byte tileable, float64 renorm, 512 B - 8 KiB:  rows_bulk (bulk-async ring)
+//   16-byte tileable, 8 KiB - 112 KiB:                rows_wide (row in shared memory, whole block)
+//   32-byte tileable, <= 8 KiB:                       rows_reg with 256-bit accesses
+//   16-byte tileable, <= 8 KiB:                       rows_reg with 128-bit accesses
+//   anything else:                                    rows_general
 // Truncation moves bytes, so one instantiation (T = float) serves both element types.
 template <typename T, int MODE>
 int launch_dense(const void* in, void* out, int64_t batch, int64_t D, int64_t kk, cudaStream_t s) {
@@ -199,8 +230,11 @@ int launch_dense(const void* in, void* out, int64_t batch, int64_t D, int64_t kk
       return launch_bulk<T, 16, 2, MODE, false>(in, out, batch, in_pitch, nvec16, 4, D, nullptr, nullptr, s);
     }
   }
+  const bool tile16 = aligned_to(in, 16) && aligned_to(out, 16) && in_pitch % 16 == 0 && k_bytes % 16 == 0;
+  if (tile16 && k_bytes > 8192 && k_bytes <= kWideMaxRowBytes)
+    return launch_wide<T, MODE>(in, out, batch, in_pitch, (int)(k_bytes / 16), s);
   if (aligned_to(in, 32) && aligned_to(out, 32) && in_pitch % 32 == 0 && k_bytes % 32 == 0 &&
-      k_bytes <= 64 * 1024) {
+      k_bytes <= 8192) {
     const int nvec = (int)(k_bytes / 32);
     const int nv = (nvec + 31) / 32;
     // short rows: 8 or 16 lanes per row, so a warp finishes 4 or 2 rows per reduction
@@ -210,13 +244,10 @@ int launch_dense(const void* in, void* out, int64_t batch, int64_t D, int64_t kk
     if (nv <= 1) return launch_reg<TT, 32, 1, R1, 32, MODE, MB, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
     if (nv <= 2) return launch_reg<TT, 32, 2, R2, 32, MODE, MB, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
     if (nv <= 4) return launch_reg<TT, 32, 4, 1, 32, MODE, MB4, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
-    if (nv <= 8) {
-      if constexpr (heavy) return launch_reg<TT, 32, 8, 1, 32, MODE, MB8, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
-      else return launch_coop<TT, 32, 4, 2, MODE, 4>(in, out, batch, in_pitch, nvec, s);
-    }
-    if (nv <= 16) return launch_coop<TT, 32, 4, 4, MODE, MB4>(in, out, batch, in_pitch, nvec, s);
-    if (nv <= 32) return launch_coop<TT, 32, 4, 8, MODE, MB4>(in, out, batch, in_pitch, nvec, s);
-    return launch_coop<TT, 32, 8, 8, MODE, MB8>(in, out, batch, in_pitch, nvec, s);
+    // 4-8 KiB rows: float32 renorm does as well through the bulk ring (6.79 vs 6.65 TB/s)
+    if constexpr (MODE == kModeRenorm && !heavy)
+      return launch_bulk<T, 16, 2, MODE, false>(in, out, batch, in_pitch, (int)(k_bytes / 16), 4, D, nullptr, nullptr, s);
+    return launch_reg<TT, 32, 8, 1, 32, MODE, MB8, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
   }
   if (aligned_to(in, 16) && aligned_to(out, 16) && in_pitch % 16 == 0 && k_bytes % 16 == 0 &&
       k_bytes <= 16 * 512) {

@@ -4,13 +4,15 @@
 // (/root/reference/core/internal/api/handlers.go:2068-2076) on a packed row-major matrix:
 // keep the first k of D components of every row and, in RENORM mode, divide them by their
 // L2 norm.  It is a bandwidth-bound streaming reduction (3 flops per 2*sizeof(T) bytes), so
-// there are no tensor cores here.  Every kernel reads only the k-prefix of a row, keeps the
-// whole prefix in registers between its one load and its one store, and reduces with warp
-// shuffles:
+// there are no tensor cores here.  Every kernel reads only the k-prefix of a row, once, keeps
+// it on chip (registers or shared memory) until its one store, and reduces with warp shuffles:
 //
-//   rows_reg_kernel   one warp owns R whole rows (prefix <= 8 KiB), 256-bit LDG/STG
-//   rows_coop_kernel  G warps of a block share one row (prefix <= 64 KiB), partial sums
-//                     meet in shared memory behind a named barrier
+//   rows_reg_kernel   a warp (or 8/16 lanes of it) owns whole rows (prefix <= 8 KiB), 256-bit
+//                     LDG/STG, the prefix lives in registers between its load and its store
+//   rows_bulk_kernel  the prefix comes in through a per-warp shared-memory ring filled by
+//                     cp.async.bulk + mbarrier (TMA), for float64 renorm (long arithmetic)
+//   rows_ring_kernel  ragged batches: the same ring handed out in 512-byte pages
+//   rows_wide_kernel  8 KiB - 112 KiB prefixes: the block shares a row held in shared memory
 //   rows_general_kernel  any k / D / element alignment, two passes, second from L1/L2
 //
 // Numerics (bar: <= 4 ulp of the exactly rounded quotient; documented: <= 2 ulp):
@@ -431,100 +433,6 @@ rows_reg_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t bat
   }
 }
 
-// ---------------------------------------------------- cooperative-row kernel ----
-// G warps of a block share one row: vector slot j of warp g covers vectors
-// [(j*G + g)*32, (j*G + g + 1)*32) of the prefix, so a short prefix still spreads evenly.  Per-warp partial sums meet in shared memory behind a named barrier that
-// only the group's G*32 threads use, so groups (and their rare slow paths) never wait for
-// each other.  Prefix up to G*NV*32*VB bytes (64 KiB at G = 8, NV = 8, VB = 32).
-__device__ __forceinline__ void group_sync(int id, int nthreads) {
-  asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(nthreads) : "memory");
-}
-
-template <typename T, int VB, int NV, int G, int MODE, int MINB, int HINT>
-__global__ void __launch_bounds__(kThreads, MINB)
-rows_coop_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t batch,
-                 int64_t in_pitch /*bytes*/, int nvec) {
-  constexpr int W = VB / 4, NW = NV * W;
-  constexpr int RPB = kWarpsPerBlock / G;            // rows per block iteration
-  __shared__ double part[2][kWarpsPerBlock][3];      // double-buffered: (s, c, max)
-  pdl_prologue();
-  const int lane = threadIdx.x & 31;
-  const int wib = threadIdx.x >> 5;                  // warp in block
-  const int grp = wib / G, g = wib % G;
-  const int bar_id = 1 + grp;
-  const int64_t out_pitch = (int64_t)nvec * VB;
-  int ph = 0;
-
-  for (int64_t row = (int64_t)blockIdx.x * RPB + grp; row < batch; row += (int64_t)gridDim.x * RPB) {
-    uint32_t w[NW];
-    const char* src = in + row * in_pitch;
-    char* dst = out + row * out_pitch;
-#pragma unroll
-    for (int j = 0; j < NV; ++j) {
-      const int idx = (j * G + g) * 32 + lane;
-      if (idx < nvec) {
-        ld_vec<VB, HINT>(&w[j * W], src + (int64_t)idx * VB);
-      } else {
-#pragma unroll
-        for (int q = 0; q < W; ++q) w[j * W + q] = 0u;
-      }
-    }
-
-    if constexpr (MODE == kModeRenorm) {
-      // exchange partials of the group; every warp then sums them in the same order
-      auto exchange = [&](double s, double c, double m, Acc2& tot, double& mx) {
-        if (lane == 0) { part[ph][wib][0] = s; part[ph][wib][1] = c; part[ph][wib][2] = m; }
-        group_sync(bar_id, G * 32);
-        tot.clear(); mx = 0.0;
-#pragma unroll
-        for (int i = 0; i < G; ++i) {
-          tot.merge(part[ph][grp * G + i][0], part[ph][grp * G + i][1]);
-          mx = fmax(mx, part[ph][grp * G + i][2]);
-        }
-        ph ^= 1;                                       // next exchange uses the other buffer
-      };
-      if constexpr (sizeof(T) == 4) {
-        const double a = warp_sum(lane_sumsq32<NW>(w));
-        Acc2 tot; double mx;
-        exchange(a, 0.0, 0.0, tot, mx);
-        Scale32 sc; sc.from_ss(tot.s + tot.c);
-        lane_apply32<NW>(w, sc);
-      } else {
-        Acc2 acc;
-        lane_sumsq64<NW>(w, 0, acc);
-        acc.warp_reduce();
-        const double m = warp_max(lane_maxabs64<NW>(w));
-        Acc2 tot; double mx;
-        exchange(acc.s, acc.c, m, tot, mx);
-        Scale64 sc; sc.pre = 0; sc.kind = kFast;
-        double hi, lo;
-        tot.split(hi, lo);
-        if (ss_in_range(hi)) {
-          sc.from_ss(hi, lo);
-        } else if (!(mx > 0.0) || !(mx <= DBL_MAX)) {
-          sc.kind = kCopy;
-        } else {                                       // group-uniform slow path
-          sc.kind = kSlow;
-          sc.pre = -ilogb(mx);
-          lane_sumsq64<NW>(w, sc.pre, acc);
-          acc.warp_reduce();
-          double mx2;
-          exchange(acc.s, acc.c, 0.0, tot, mx2);
-          tot.split(hi, lo);
-          sc.from_ss(hi, lo);
-        }
-        lane_apply64<NW>(w, sc);
-      }
-    }
-
-#pragma unroll
-    for (int j = 0; j < NV; ++j) {
-      const int idx = (j * G + g) * 32 + lane;
-      if (idx < nvec) st_vec<VB, HINT>(dst + (int64_t)idx * VB, &w[j * W]);
-    }
-  }
-}
-
 // ------------------------------------------------------ bulk-async row kernel ----
 // For rows whose arithmetic is long enough to expose memory latency (float64 renorm): the
 // row prefix travels global -> shared memory as ONE bulk asynchronous copy (cp.async.bulk,
@@ -855,6 +763,154 @@ rows_ring_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t ba
     }
     __syncwarp();                                       // every lane is done with the pages
     if (lane == 0) { used -= held; --inflight; issue_more(); }
+  }
+}
+
+// ------------------------------------------------------------ wide-row kernel ----
+// Prefixes from 8 KiB to 112 KiB: the whole block shares a row.  The row travels global ->
+// shared memory by bulk-async copies (16 KiB pieces on one mbarrier) into one of two buffers,
+// so the next row is in flight while this one is reduced; the 8 warps sum their slices out of
+// shared memory, meet once behind __syncthreads, and write the scaled row straight to global
+// memory in a second pass over shared memory.  Registers stay small whatever the row length.
+// A block owns rows_per_block consecutive rows.
+template <typename T, int MODE>
+__global__ void __launch_bounds__(kThreads)
+rows_wide_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t batch,
+                 int64_t in_pitch /*bytes*/, int nvec16, int rows_per_block) {
+  extern __shared__ __align__(128) unsigned char wide[];
+  __shared__ uint64_t bars[2];
+  __shared__ double part[kWarpsPerBlock][3];
+  const int tid = threadIdx.x, lane = tid & 31, wib = tid >> 5;
+  const uint32_t row_bytes = (uint32_t)nvec16 * 16u;
+  const uint32_t buf_stride = (row_bytes + 127u) & ~127u;
+  const uint32_t bar0 = smem_u32(&bars[0]);
+  if (tid == 0) {
+    mbar_init(bar0, 1); mbar_init(bar0 + 8u, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  __syncthreads();
+  pdl_prologue();
+
+  uint64_t policy;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+  const int64_t r1 = r0 + rows_per_block < batch ? r0 + rows_per_block : batch;
+  auto issue = [&](int64_t row, int b) {                // thread 0 only
+    const uint32_t bar = bar0 + 8u * b;
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(row_bytes) : "memory");
+    const char* src = in + row * in_pitch;
+    const uint32_t dst = smem_u32(wide + (size_t)b * buf_stride);
+    for (uint32_t off = 0; off < row_bytes; off += 16384u) {
+      const uint32_t n = row_bytes - off < 16384u ? row_bytes - off : 16384u;
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+                   " [%0], [%1], %2, [%3], %4;"
+                   :: "r"(dst + off), "l"(src + off), "r"(n), "r"(bar), "l"(policy) : "memory");
+    }
+  };
+  if (tid == 0) {
+    if (r0 < r1) issue(r0, 0);
+    if (r0 + 1 < r1) issue(r0 + 1, 1);
+  }
+  uint32_t parity = 0;
+  for (int64_t row = r0; row < r1; ++row) {
+    const int b = (int)((row - r0) & 1);
+    mbar_wait(bar0 + 8u * b, (parity >> b) & 1u);
+    parity ^= 1u << b;
+    const uint4* src = reinterpret_cast<const uint4*>(wide + (size_t)b * buf_stride);
+    uint4* dst4 = reinterpret_cast<uint4*>(out + row * (int64_t)row_bytes);
+
+    if constexpr (MODE == kModeTruncate) {
+      for (int i = tid; i < nvec16; i += kThreads) { const uint4 v = src[i]; st_vec<16, 0>(dst4 + i, &v.x); }
+    } else if constexpr (sizeof(T) == 4) {
+      double a = 0.0;
+      for (int i = tid; i < nvec16; i += kThreads) {
+        const uint4 v = src[i];
+        const double x0 = (double)__uint_as_float(v.x), x1 = (double)__uint_as_float(v.y);
+        const double x2 = (double)__uint_as_float(v.z), x3 = (double)__uint_as_float(v.w);
+        a = fma(x0, x0, a); a = fma(x1, x1, a); a = fma(x2, x2, a); a = fma(x3, x3, a);
+      }
+      a = warp_sum(a);
+      if (lane == 0) part[wib][0] = a;
+      __syncthreads();
+      double ss = 0.0;
+#pragma unroll
+      for (int w = 0; w < kWarpsPerBlock; ++w) ss += part[w][0];
+      Scale32 sc; sc.from_ss(ss);
+      for (int i = tid; i < nvec16; i += kThreads) {
+        uint4 v = src[i];
+        if (sc.kind != kCopy) {
+          v.x = __float_as_uint(sc.apply(__uint_as_float(v.x))); v.y = __float_as_uint(sc.apply(__uint_as_float(v.y)));
+          v.z = __float_as_uint(sc.apply(__uint_as_float(v.z))); v.w = __float_as_uint(sc.apply(__uint_as_float(v.w)));
+        }
+        st_vec<16, 0>(dst4 + i, &v.x);
+      }
+    } else {
+      // blocks of <= 4 squares (two 16-byte vectors of this thread), block sums added error-free
+      auto block_sumsq = [&](int pre, Acc2& tot) {
+        Acc2 acc; acc.clear();
+        for (int i = tid; i < nvec16; i += 2 * kThreads) {
+          const uint4 v = src[i];
+          double x0 = words_to_double(&v.x), x1 = words_to_double(&v.z);
+          if (pre != 0) { x0 = scalbn(x0, pre); x1 = scalbn(x1, pre); }
+          double q = fma(x1, x1, x0 * x0);
+          if (i + kThreads < nvec16) {
+            const uint4 u = src[i + kThreads];
+            double x2 = words_to_double(&u.x), x3 = words_to_double(&u.z);
+            if (pre != 0) { x2 = scalbn(x2, pre); x3 = scalbn(x3, pre); }
+            q = fma(x2, x2, q); q = fma(x3, x3, q);
+          }
+          acc.add(q);
+        }
+        acc.warp_reduce();
+        __syncthreads();                                 // part[] free again (second round)
+        if (lane == 0) { part[wib][0] = acc.s; part[wib][1] = acc.c; }
+        __syncthreads();
+        tot.clear();
+#pragma unroll
+        for (int w = 0; w < kWarpsPerBlock; ++w) tot.merge(part[w][0], part[w][1]);
+      };
+      Acc2 tot;
+      block_sumsq(0, tot);
+      Scale64 sc; sc.pre = 0; sc.kind = kFast; sc.r = 0.0; sc.r_lo = 0.0;
+      double hi, lo;
+      tot.split(hi, lo);
+      if (ss_in_range(hi)) {                            // block-uniform: every thread holds the same total
+        sc.from_ss(hi, lo);
+      } else {
+        double m = 0.0;
+        for (int i = tid; i < nvec16; i += kThreads) {
+          const uint4 v = src[i];
+          m = fmax(m, fmax(fabs(words_to_double(&v.x)), fabs(words_to_double(&v.z))));
+        }
+        m = warp_max(m);
+        __syncthreads();
+        if (lane == 0) part[wib][2] = m;
+        __syncthreads();
+        m = 0.0;
+#pragma unroll
+        for (int w = 0; w < kWarpsPerBlock; ++w) m = fmax(m, part[w][2]);
+        if (!(m > 0.0) || !(m <= DBL_MAX)) {
+          sc.kind = kCopy;
+        } else {
+          sc.kind = kSlow;
+          sc.pre = -ilogb(m);
+          block_sumsq(sc.pre, tot);
+          tot.split(hi, lo);
+          sc.from_ss(hi, lo);
+        }
+      }
+      for (int i = tid; i < nvec16; i += kThreads) {
+        uint4 v = src[i];
+        if (sc.kind != kCopy) {
+          double_to_words(&v.x, sc.apply(words_to_double(&v.x)));
+          double_to_words(&v.z, sc.apply(words_to_double(&v.z)));
+        }
+        st_vec<16, 0>(dst4 + i, &v.x);
+      }
+    }
+    __syncthreads();                                     // everyone is done with buffer b
+    if (tid == 0 && row + 2 < r1) issue(row + 2, b);
   }
 }
 

@@ -65,24 +65,6 @@ void run_reg(const Shape& s, const void* in, void* out, Timer& tm, int waves = 1
   printf("%-78s %8.3f ms %8.1f GB/s  regs=%d occ=%d grid=%d\n", name, ms, gbs, fa.numRegs, per_sm, grid);
 }
 
-template <typename T, int VB, int NV, int G, int MODE, int MINB, int HINT>
-void run_coop(const Shape& s, const void* in, void* out, Timer& tm, int waves = 0) {
-  char name[128];
-  snprintf(name, sizeof name, "%s coop<VB=%d,NV=%d,G=%d,mode=%d,minb=%d,hint=%d,w=%d>", s.name, VB, NV, G, MODE, MINB, HINT, waves);
-  if (!want(name)) return;
-  auto kern = rows_coop_kernel<T, VB, NV, G, MODE, MINB, HINT>;
-  int per_sm = 0;
-  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kThreads, 0));
-  cudaFuncAttributes fa; CK(cudaFuncGetAttributes(&fa, kern));
-  const int64_t need = (s.rows + kWarpsPerBlock / G - 1) / (kWarpsPerBlock / G);
-  const int grid = waves > 0 ? (int)std::min<int64_t>(need, (int64_t)g_sms * per_sm * waves) : (int)need;
-  const int nvec = (int)(s.k * s.es / VB);
-  double ms = tm.ms([&](int) { kern<<<grid, kThreads>>>((const char*)in, (char*)out, s.rows, s.D * s.es, nvec); }, 3, g_iters);
-  CK(cudaGetLastError());
-  double gbs = (double)s.rows * 2 * s.k * s.es / ms / 1e6;
-  printf("%-78s %8.3f ms %8.1f GB/s  regs=%d occ=%d grid=%d\n", name, ms, gbs, fa.numRegs, per_sm, grid);
-}
-
 template <typename T, int NV16, int S, int NCW, int MODE>
 void run_bulk(const Shape& s, const void* in, void* out, Timer& tm, const void* ref_out = nullptr, int rpw = 0) {
   char name[128];
@@ -107,6 +89,36 @@ void run_bulk(const Shape& s, const void* in, void* out, Timer& tm, const void* 
     same = memcmp(a.data(), b.data(), out_bytes) == 0;
   }
   printf("%-78s %8.3f ms %8.1f GB/s  regs=%d smem=%zuK same_as_reg=%d\n", name, ms, gbs, fa.numRegs, smem >> 10, same);
+}
+
+template <typename T, int MODE>
+void run_wide(const Shape& s, const void* in, void* out, Timer& tm, int rpb) {
+  char name[128];
+  snprintf(name, sizeof name, "%s wide<mode=%d,rpb=%d>", s.name, MODE, rpb);
+  if (!want(name)) return;
+  auto kern = rows_wide_kernel<T, MODE>;
+  const int nvec16 = (int)(s.k * s.es / 16);
+  const size_t stride = ((size_t)nvec16 * 16 + 127) & ~(size_t)127;
+  const size_t smem = 2 * stride;
+  CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 0;
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kThreads, smem));
+  cudaFuncAttributes fa; CK(cudaFuncGetAttributes(&fa, kern));
+  const int grid = (int)((s.rows + rpb - 1) / rpb);
+  double ms = tm.ms([&](int) { kern<<<grid, kThreads, smem>>>((const char*)in, (char*)out, s.rows, s.D * s.es, nvec16, rpb); }, 3, g_iters);
+  CK(cudaGetLastError());
+  double gbs = (double)s.rows * 2 * s.k * s.es / ms / 1e6;
+  printf("%-78s %8.3f ms %8.1f GB/s  regs=%d occ=%d smem=%zuK\n", name, ms, gbs, fa.numRegs, per_sm, smem >> 10);
+}
+
+// max relative difference between two outputs (different summation orders differ in the last bit)
+template <typename T> double max_rel_diff(const void* a, const void* b, size_t n) {
+  std::vector<T> ha(n), hb(n);
+  CK(cudaMemcpy(ha.data(), a, n * sizeof(T), cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(hb.data(), b, n * sizeof(T), cudaMemcpyDeviceToHost));
+  double m = 0;
+  for (size_t i = 0; i < n; ++i) { double d = fabs((double)ha[i] - (double)hb[i]) / (fabs((double)hb[i]) + 1e-300); if (d > m) m = d; }
+  return m;
 }
 
 // PCIe study for the host path: DMA ceilings, prefix-only 2-D DMA, and the kernels reading and
@@ -225,13 +237,11 @@ int main(int argc, char** argv) {
   }
 
   std::vector<Shape> shapes = {
-      {"C3f32 1Mx4096->1024", 1048576, 4096, 1024, 4},
-      {"C4f32 2Mx3072->256", 2097152, 3072, 256, 4},
-      {"C3f64 1Mx4096->1024", 1048576, 4096, 1024, 8},
-      {"K768f64 512Kx3072->768", 524288, 3072, 768, 8},
-      {"K512f64 1Mx4096->512", 1048576, 4096, 512, 8},
-      {"K256f64 1Mx4096->256", 1048576, 4096, 256, 8},
-      {"K128f64 2Mx4096->128", 2097152, 4096, 128, 8},
+      {"MIDf64 256Kx3072->1536", 262144, 3072, 1536, 8},
+      {"BIGf64 128Kx4096->4096", 131072, 4096, 4096, 8},
+      {"BIGf32 256Kx4096->4096", 262144, 4096, 4096, 4},
+      {"HUGEf32 64Kx16384->16384", 65536, 16384, 16384, 4},
+      {"WIDEf64 32Kx16384->12288", 32768, 16384, 12288, 8},
   };
   for (const Shape& s : shapes) {
     void *in, *out;
@@ -242,35 +252,20 @@ int main(int argc, char** argv) {
     CK(cudaDeviceSynchronize());
     const int64_t kb = s.k * s.es;
     void* out2; CK(cudaMalloc(&out2, (size_t)s.rows * s.k * s.es));
-    // register kernel vs bulk-async ring kernel (persistent and one-shot), sustained (ITERS=100)
-    if (s.es == 4 && kb == 4096) {
-      run_reg<float, 32, 4, 1, 1, 4, 1>(s, in, out, tm, 1);
-      run_reg<float, 32, 4, 1, 1, 4, 1>(s, in, out, tm, 0);
-      run_bulk<float, 8, 2, 8, 1>(s, in, out2, tm, out, 0);
-      run_bulk<float, 8, 2, 8, 1>(s, in, out2, tm, out, 8);
-    } else if (s.es == 4 && kb == 1024) {
-      run_reg<float, 32, 1, 4, 1, 4, 1>(s, in, out, tm, 0);
-      run_bulk<float, 2, 4, 4, 1>(s, in, out2, tm, out, 16);
-    } else if (s.es == 8 && kb == 8192) {
-      run_reg<double, 32, 8, 1, 1, 2, 1>(s, in, out, tm, 0);
-      run_coop<double, 32, 4, 2, 1, 3, 1>(s, in, out2, tm, 0);
-      run_bulk<double, 16, 2, 8, 1>(s, in, out2, tm, out, 0);
-      run_bulk<double, 16, 3, 8, 1>(s, in, out2, tm, out, 0);
-      run_bulk<double, 16, 2, 4, 1>(s, in, out2, tm, out, 4);
-      run_bulk<double, 16, 2, 4, 1>(s, in, out2, tm, out, 8);
-      run_bulk<double, 16, 2, 4, 0>(s, in, out2, tm, nullptr, 4);
-    } else if (s.es == 8 && kb == 6144) {
-      run_reg<double, 32, 8, 1, 1, 2, 1>(s, in, out, tm, 0);
-      run_bulk<double, 12, 2, 4, 1>(s, in, out2, tm, out, 4);
-    } else if (s.es == 8 && kb == 4096) {
-      run_reg<double, 32, 4, 1, 1, 3, 1>(s, in, out, tm, 0);
-      run_bulk<double, 8, 2, 4, 1>(s, in, out2, tm, out, 4);
-    } else if (s.es == 8 && kb == 2048) {
-      run_reg<double, 32, 2, 1, 1, 4, 1>(s, in, out, tm, 0);
-      run_bulk<double, 4, 2, 4, 1>(s, in, out2, tm, out, 8);
-    } else if (s.es == 8 && kb == 1024) {
-      run_reg<double, 32, 1, 4, 1, 4, 1>(s, in, out, tm, 0);
-      run_bulk<double, 2, 4, 4, 1>(s, in, out2, tm, out, 8);
+    // cooperative register kernel vs wide-row shared-memory kernel
+    const size_t nel = (size_t)s.rows * s.k;
+    if (s.es == 8 && kb == 12288) {
+      for (int rpb : {2, 4, 8}) run_wide<double, 1>(s, in, out2, tm, rpb);
+      run_wide<double, 0>(s, in, out2, tm, 4);
+    } else if (s.es == 8 && kb == 32768) {
+      for (int rpb : {2, 4, 8}) run_wide<double, 1>(s, in, out2, tm, rpb);
+    } else if (s.es == 4 && kb == 16384) {
+      for (int rpb : {2, 4, 8}) run_wide<float, 1>(s, in, out2, tm, rpb);
+    } else if (s.es == 4 && kb == 65536) {
+      for (int rpb : {2, 4}) run_wide<float, 1>(s, in, out2, tm, rpb);
+    } else if (s.es == 8 && kb == 98304) {
+      for (int rpb : {2, 4}) run_wide<double, 1>(s, in, out2, tm, rpb);
+      run_wide<double, 0>(s, in, out2, tm, 4);
     }
     CK(cudaFree(out2));
     CK(cudaFree(in)); CK(cudaFree(out));
