@@ -202,3 +202,26 @@ def test_json_packer_base64_renorm(oracle):
         b = np.frombuffer(base64.b64decode(want), dtype="<f4")
         _ulp(oracle, a.copy(), b.copy())
     _ulp(oracle, np.array(got[40]["embedding"]), oracle.renorm_exact(np.array([items[40]["embedding"]]), 1024)[0])
+
+
+def test_host_path_concurrent_handlers(oracle):
+    """Many handler threads at once (one goroutine per connection in the reference): calls on
+    one device queue behind its lock and every caller gets its own rows back."""
+    import threading
+    inputs = [oracle.fill(40 + t, 3000 + 17 * t, 1024, np.float32) for t in range(6)]
+    wants = [oracle.renorm_exact(x, 256) for x in inputs]
+    errs = []
+
+    def worker(t):
+        try:
+            for _ in range(5):
+                got = eg.truncate_norm_host(inputs[t], 256)
+                d, _ = oracle.max_ulp(got, wants[t])
+                assert 0 <= d <= 2, d
+        except Exception as e:  # noqa: BLE001
+            errs.append((t, e))
+
+    th = [threading.Thread(target=worker, args=(t,)) for t in range(6)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not errs, errs
