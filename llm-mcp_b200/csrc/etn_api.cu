@@ -197,11 +197,16 @@ int launch_general(const void* in, void* out, int64_t batch, int64_t D, int64_t 
   return launch_kernel(kern, grid, s, (const T*)in, (T*)out, batch, D, k, k_per_row, out_offsets);
 }
 
+template <typename T, int MODE>
+int launch_ring(const void* in, void* out, int64_t batch, int64_t D, int64_t k_dense, const int32_t* k_per_row,
+                const int64_t* out_offsets, cudaStream_t s);
+
 // Dense rows.  Kernel choice by prefix size and alignment:
 //   16-byte tileable, float64 renorm, 512 B - 8 KiB:  rows_bulk (bulk-async ring)
 //   16-byte tileable, 8 KiB - 112 KiB:                rows_wide (row in shared memory, whole block)
 //   32-byte tileable, <= 8 KiB:                       rows_reg with 256-bit accesses
 //   16-byte tileable, <= 8 KiB:                       rows_reg with 128-bit accesses
+//   16-byte aligned input rows, odd k, <= 8 KiB:      rows_ring (staged rounded up, element-wise)
 //   anything else:                                    rows_general
 // Truncation moves bytes, so one instantiation (T = float) serves both element types.
 template <typename T, int MODE>
@@ -261,6 +266,9 @@ int launch_dense(const void* in, void* out, int64_t batch, int64_t D, int64_t kk
     if (nv <= 8) return launch_reg<TT, 16, 8, 1, 32, MODE, MB4, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
     return launch_reg<TT, 16, 16, 1, 32, MODE, MB8, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
   }
+  // prefix not 16-byte tileable (odd k) but 16-byte aligned input rows: staged through the ring
+  if (aligned_to(in, 16) && in_pitch % 16 == 0 && k_bytes <= 8192 - 16)
+    return launch_ring<T, MODE>(in, out, batch, D, kk, nullptr, nullptr, s);
   return launch_general<T, MODE>(in, out, batch, D, kk, nullptr, nullptr, s);
 }
 
@@ -269,11 +277,11 @@ int launch_dense(const void* in, void* out, int64_t batch, int64_t D, int64_t kk
 // still keep the ring full; rows that are not 16-byte tileable or exceed 8 KiB fall back
 // inside the kernel.
 template <typename T, int MODE>
-int launch_ragged(const void* in, void* out, int64_t batch, int64_t D, const int32_t* k_per_row,
-                  const int64_t* out_offsets, cudaStream_t s) {
+int launch_ring(const void* in, void* out, int64_t batch, int64_t D, int64_t k_dense, const int32_t* k_per_row,
+                const int64_t* out_offsets, cudaStream_t s) {
   const int64_t in_pitch = D * (int64_t)sizeof(T);
-  if (!(aligned_to(in, 16) && aligned_to(out, 16) && in_pitch % 16 == 0))
-    return launch_general<T, MODE>(in, out, batch, D, 0, k_per_row, out_offsets, s);
+  if (!(aligned_to(in, 16) && in_pitch % 16 == 0))
+    return launch_general<T, MODE>(in, out, batch, D, k_dense, k_per_row, out_offsets, s);
   constexpr int NCW = 4;
   constexpr size_t smem = (size_t)NCW * 8192 + (size_t)NCW * 8 * 8 + (size_t)NCW * 8 * 3 * 4;
   auto kern = rows_ring_kernel<T, NCW, MODE>;
@@ -304,8 +312,14 @@ int launch_ragged(const void* in, void* out, int64_t batch, int64_t D, const int
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
-  return counted_launch(cudaLaunchKernelEx(&cfg, kern, (const char*)in, (char*)out, batch, in_pitch, rpw, D,
+  return counted_launch(cudaLaunchKernelEx(&cfg, kern, (const char*)in, (char*)out, batch, in_pitch, rpw, D, k_dense,
                                            k_per_row, out_offsets));
+}
+
+template <typename T, int MODE>
+int launch_ragged(const void* in, void* out, int64_t batch, int64_t D, const int32_t* k_per_row,
+                  const int64_t* out_offsets, cudaStream_t s) {
+  return launch_ring<T, MODE>(in, out, batch, D, 0, k_per_row, out_offsets, s);
 }
 
 int check_dense(int64_t batch, int64_t D, int64_t k, int dtype, const void* in, const void* out) {

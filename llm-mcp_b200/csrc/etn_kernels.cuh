@@ -602,11 +602,14 @@ rows_bulk_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t ba
 // rolled passes, so the instruction count follows the row's real length and the kernel needs
 // few registers (a register-resident version sized for the longest row ran 777 instructions
 // per row at 12 warps per SM and was issue-bound at 3.1-3.7 TB/s).
-// A row that is not 16-byte tileable or is longer than the ring takes general_row.
+// Only the input rows have to be 16-byte aligned: a prefix that is not a multiple of 16
+// bytes is staged rounded up and processed element-wise.  Dense batches with such a k use
+// this kernel too (k_per_row == out_offsets == nullptr).  A row longer than the ring takes
+// general_row.
 template <typename T, int NCW, int MODE>
 __global__ void __launch_bounds__(NCW * 32, 6)
 rows_ring_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t batch,
-                 int64_t in_pitch /*bytes*/, int rows_per_warp, int64_t D,
+                 int64_t in_pitch /*bytes*/, int rows_per_warp, int64_t D, int64_t k_dense,
                  const int32_t* __restrict__ k_per_row, const int64_t* __restrict__ out_offsets) {
   constexpr int PAGE = 512, P = 16, R = 8;             // 8 KiB ring per warp
   constexpr int RING = PAGE * P;
@@ -628,14 +631,16 @@ rows_ring_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t ba
   __syncthreads();
   pdl_prologue();
 
+  // Bytes of row `row` to stage: its prefix rounded up to 16 (the input rows are 16-byte
+  // aligned and pitched, so the round-up stays inside the row), or 0 when it does not fit
+  // the ring.  k_per_row == nullptr: every row keeps k_dense; out_offsets == nullptr: dense.
   auto row_plan = [&](int64_t row, char*& dst, int64_t& kr) -> uint32_t {
-    kr = k_per_row[row];
+    kr = k_per_row ? (int64_t)k_per_row[row] : k_dense;
     if (kr > D) kr = D;
     const int64_t kb = kr * (int64_t)sizeof(T);
-    dst = out + out_offsets[row] * (int64_t)sizeof(T);
-    const bool tile = kb > 0 && (kb % 16 == 0) && kb <= (int64_t)RING &&
-                      (reinterpret_cast<uintptr_t>(dst) % 16) == 0;
-    return tile ? (uint32_t)kb : 0u;
+    dst = out + (out_offsets ? out_offsets[row] : row * kr) * (int64_t)sizeof(T);
+    const int64_t staged = (kb + 15) & ~(int64_t)15;
+    return (kb > 0 && staged <= (int64_t)RING) ? (uint32_t)staged : 0u;
   };
 
   uint64_t policy;
@@ -689,8 +694,64 @@ rows_ring_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t ba
     const int nvec16 = (int)(row_bytes >> 4);
     const uint4* src = reinterpret_cast<const uint4*>(my_ring + pos * PAGE);
     uint4* dst4 = reinterpret_cast<uint4*>(dst);
+    const bool vec_ok = ((kr * (int64_t)sizeof(T)) % 16 == 0) && (reinterpret_cast<uintptr_t>(dst) % 16) == 0;
 
-    if constexpr (MODE == kModeTruncate) {
+    if (!vec_ok) {
+      // odd k, or an output row that is not 16-byte aligned: same two passes over the staged
+      // row, element by element (coalesced 4/8-byte accesses)
+      const T* xs = reinterpret_cast<const T*>(src);
+      T* y = reinterpret_cast<T*>(dst);
+      const int n = (int)kr;
+      if constexpr (MODE == kModeTruncate) {
+        for (int i = lane; i < n; i += 32) y[i] = xs[i];
+      } else if constexpr (sizeof(T) == 4) {
+        double a = 0.0;
+        for (int i = lane; i < n; i += 32) { const double xv = (double)xs[i]; a = fma(xv, xv, a); }
+        Scale32 sc; sc.from_ss(warp_sum(a));
+        if (sc.kind == kCopy) { for (int i = lane; i < n; i += 32) y[i] = xs[i]; }
+        else { for (int i = lane; i < n; i += 32) y[i] = sc.apply(xs[i]); }
+      } else {
+        auto sumsq_e = [&](int pre, Acc2& acc) {
+          acc.clear();
+          for (int i = lane; i < n; i += 128) {
+            double q = 0.0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              if (i + 32 * j < n) {
+                double xv = (double)xs[i + 32 * j];
+                if (pre != 0) xv = scalbn(xv, pre);
+                q = fma(xv, xv, q);
+              }
+            }
+            acc.add(q);
+          }
+          acc.warp_reduce();
+        };
+        Acc2 acc;
+        sumsq_e(0, acc);
+        Scale64 sc; sc.pre = 0; sc.kind = kFast; sc.r = 0.0; sc.r_lo = 0.0;
+        double hi, lo;
+        acc.split(hi, lo);
+        if (ss_in_range(hi)) {
+          sc.from_ss(hi, lo);
+        } else {
+          double m = 0.0;
+          for (int i = lane; i < n; i += 32) m = fmax(m, fabs((double)xs[i]));
+          m = warp_max(m);
+          if (!(m > 0.0) || !(m <= DBL_MAX)) {
+            sc.kind = kCopy;
+          } else {
+            sc.kind = kSlow;
+            sc.pre = -ilogb(m);
+            sumsq_e(sc.pre, acc);
+            acc.split(hi, lo);
+            sc.from_ss(hi, lo);
+          }
+        }
+        if (sc.kind == kCopy) { for (int i = lane; i < n; i += 32) y[i] = xs[i]; }
+        else { for (int i = lane; i < n; i += 32) y[i] = (T)sc.apply((double)xs[i]); }
+      }
+    } else if constexpr (MODE == kModeTruncate) {
       for (int i = lane; i < nvec16; i += 32) { const uint4 v = src[i]; st_vec<16, 0>(dst4 + i, &v.x); }
     } else if constexpr (sizeof(T) == 4) {
       double a = 0.0;

@@ -93,6 +93,10 @@ SHAPES = [
     (257, 3072, 1536, np.float64, 15), (257, 4096, 4096, np.float32, 15), (129, 4096, 4096, np.float64, 15),
     (65, 8192, 8192, np.float64, 15), (65, 16384, 16384, np.float32, 15), (33, 20000, 20000, np.float32, 15),
     (129, 4096, 3000, np.float32, 15), (129, 4096, 1100, np.float64, 15),
+    # odd k on 16-byte aligned rows: staged through the ring, element-wise
+    (3001, 4096, 257, np.float64, 17), (3001, 4096, 1001, np.float64, 17), (3001, 3072, 1001, np.float32, 17),
+    (3001, 4096, 1, np.float64, 17), (3001, 4096, 1021, np.float64, 17), (3001, 4096, 2043, np.float32, 17),
+    (3001, 4096, 1023, np.float64, 17), (3001, 4096, 2047, np.float32, 17), (77, 4096, 1025, np.float64, 17),
     # wide-row kernel edges: just over 8 KiB, 96 KiB, the 112 KiB limit, one element past it
     (67, 4096, 2052, np.float32, 16), (35, 14336, 12288, np.float64, 16), (19, 28672, 28672, np.float32, 16),
     (19, 28680, 28676, np.float32, 16), (3, 14340, 14336, np.float64, 16), (1, 4096, 4096, np.float64, 16),
