@@ -24,6 +24,7 @@
 #include <charconv>
 #include <cmath>
 #include <cstring>
+#include <string.h>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -210,11 +211,81 @@ bool scan_embedding(Scanner& sc, int64_t dims, Span* out) {
   }
 }
 
+// Vectors are independent, so number parsing and formatting spread over host threads
+// (handlers run one goroutine per connection; a large response still deserves the cores).
+template <typename F>
+void parallel_for(size_t n, size_t grain, F f) {
+  size_t nt = std::min<size_t>(std::min<size_t>(std::thread::hardware_concurrency(), 16), n / grain);
+  if (nt <= 1) { for (size_t i = 0; i < n; ++i) f(i); return; }
+  std::vector<std::thread> th;
+  for (size_t t = 0; t < nt; ++t)
+    th.emplace_back([=] { for (size_t i = t; i < n; i += nt) f(i); });
+  for (auto& x : th) x.join();
+}
+
+// Speculative parallel pre-scan.  Nearly all bytes of a response sit inside the embedding
+// arrays, and validating them number by number is the scan's whole cost, so host threads
+// each take a slice of the text, look for `"embedding"` followed by `: [` and scan the
+// array that starts there.  The sequential skeleton scan below stays the only judge of what
+// is really a data item's embedding; when it arrives at an array it has a finished span for,
+// it jumps to the closing bracket instead of walking the numbers again.  A hit inside a
+// string or at the wrong depth is simply never asked for.
+struct PreScan {
+  std::vector<Span> spans;                         // sorted by .open
+  const Span* find(int64_t open) const {
+    auto it = std::lower_bound(spans.begin(), spans.end(), open, [](const Span& s, int64_t o) { return s.open < o; });
+    return (it != spans.end() && it->open == open) ? &*it : nullptr;
+  }
+};
+
+bool scan_embedding(Scanner& sc, int64_t dims, Span* out);
+
+void prescan(const char* json, size_t len, int64_t dims, PreScan* ps) {
+  const size_t kMin = 4u << 20;                     // not worth threads below 4 MiB
+  if (len < kMin) return;
+  const size_t nt = std::min<size_t>(std::min<size_t>(std::thread::hardware_concurrency(), 16), len / (kMin / 4));
+  if (nt <= 1) return;
+  std::vector<std::vector<Span>> found(nt);
+  std::vector<std::thread> th;
+  const size_t chunk = (len + nt - 1) / nt;
+  static const char key[] = "\"embedding\"";
+  const size_t klen = sizeof key - 1;
+  for (size_t t = 0; t < nt; ++t) {
+    th.emplace_back([&, t] {
+      const char* p = json + t * chunk;
+      const char* stop = json + std::min(len, (t + 1) * chunk);
+      const char* end = json + len;
+      while (p < stop) {
+        const char* q = (const char*)memmem(p, (size_t)(end - p) < (size_t)(stop - p) + klen ? (size_t)(end - p) : (size_t)(stop - p) + klen,
+                                           key, klen);
+        if (!q || q >= stop) break;
+        const char* r = q + klen;
+        while (r < end && (*r == ' ' || *r == '\t' || *r == '\n' || *r == '\r')) ++r;
+        if (r < end && *r == ':') {
+          ++r;
+          while (r < end && (*r == ' ' || *r == '\t' || *r == '\n' || *r == '\r')) ++r;
+          if (r < end && *r == '[') {
+            Scanner sc{json, end, r};
+            Span s;
+            if (scan_embedding(sc, dims, &s)) { found[t].push_back(s); p = sc.p; continue; }
+          }
+        }
+        p = q + klen;
+      }
+    });
+  }
+  for (auto& x : th) x.join();
+  for (auto& v : found) ps->spans.insert(ps->spans.end(), v.begin(), v.end());
+  std::sort(ps->spans.begin(), ps->spans.end(), [](const Span& a, const Span& b) { return a.open < b.open; });
+}
+
 // Finds the embedding arrays of result["data"][*]["embedding"] (handlers.go:2064-2073).
 // Returns 0, ETN_ERR_JSON for malformed input, ETN_ERR_JSON_DUP when "data" or an item's
 // "embedding" occurs twice (Go keeps the last one and drops the other on re-encode; a splice
 // cannot mimic that, the caller should take the reference path).
 int find_embeddings(const char* json, size_t len, int64_t dims, bool b64, std::vector<Span>* spans) {
+  PreScan ps;
+  prescan(json, len, dims, &ps);
   Scanner sc{json, json + len, json};
   sc.ws();
   if (sc.p >= sc.e || *sc.p != '{') {            // not an object: Go's Decode(&map) would fail earlier
@@ -251,7 +322,8 @@ int find_embeddings(const char* json, size_t len, int64_t dims, bool b64, std::v
             if (is_emb && ++emb_seen > 1) return ETN_ERR_JSON_DUP;
             if (is_emb && sc.p < sc.e && *sc.p == '[') {
               Span s;
-              if (!scan_embedding(sc, dims, &s)) return ETN_ERR_JSON;
+              if (const Span* hit = ps.find(sc.p - sc.b)) { s = *hit; sc.p = sc.b + s.close; }
+              else if (!scan_embedding(sc, dims, &s)) return ETN_ERR_JSON;
               spans->push_back(s);
             } else if (is_emb && b64 && sc.p < sc.e && *sc.p == '"') {
               Span s;
@@ -325,18 +397,6 @@ size_t format_go_float(double f, char* out) {
     if (nd > exp10 + 1) { *o++ = '.'; for (int i = exp10 + 1; i < nd; ++i) *o++ = digits[i]; }
   }
   return (size_t)(o - out);
-}
-
-// Vectors are independent, so number parsing and formatting spread over host threads
-// (handlers run one goroutine per connection; a large response still deserves the cores).
-template <typename F>
-void parallel_for(size_t n, size_t grain, F f) {
-  size_t nt = std::min<size_t>(std::min<size_t>(std::thread::hardware_concurrency(), 16), n / grain);
-  if (nt <= 1) { for (size_t i = 0; i < n; ++i) f(i); return; }
-  std::vector<std::thread> th;
-  for (size_t t = 0; t < nt; ++t)
-    th.emplace_back([=] { for (size_t i = t; i < n; i += nt) f(i); });
-  for (auto& x : th) x.join();
 }
 
 // Reusable pinned staging for the rewrite (one per thread would be better still; handlers

@@ -65,6 +65,37 @@ void run_reg(const Shape& s, const void* in, void* out, Timer& tm, int waves = 1
   printf("%-78s %8.3f ms %8.1f GB/s  regs=%d occ=%d grid=%d\n", name, ms, gbs, fa.numRegs, per_sm, grid);
 }
 
+// Request-sized launches (C2: 65,536 x 768 -> 256 f32, 128 MiB per launch): rotate over NSET
+// buffer pairs so nothing is served from L2, launch with programmatic dependent launch.
+template <typename T, int VB, int NV, int R, int MODE, int MINB, int L>
+void run_reg_small(const char* label, int64_t rows, int64_t D, int64_t k, int es, Timer& tm, bool pdl, int threads = kThreads) {
+  constexpr int NSET = 6;
+  static void* in[NSET]; static void* out[NSET]; static int64_t have = 0;
+  if (have != rows * D) {
+    for (int i = 0; i < NSET; ++i) {
+      if (in[i]) { cudaFree(in[i]); cudaFree(out[i]); }
+      CK(cudaMalloc(&in[i], (size_t)rows * D * es)); CK(cudaMalloc(&out[i], (size_t)rows * k * es));
+      fill_kernel<float><<<g_sms * 16, 256>>>((float*)in[i], 3 + i, 0, rows, D * es / 4, D * es / 4, D * es / 4);
+    }
+    have = rows * D;
+  }
+  auto kern = rows_reg_kernel<T, VB, NV, R, L, MODE, MINB, 1, false>;
+  const int64_t rpb = (threads / 32) * R * (32 / L);
+  const int grid = (int)((rows + rpb - 1) / rpb);
+  const int nvec = (int)(k * es / VB);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid); cfg.blockDim = dim3(threads);
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
+  double ms = tm.ms([&](int i) {
+    CK(cudaLaunchKernelEx(&cfg, kern, (const char*)in[i % NSET], (char*)out[i % NSET], rows, D * es, nvec, D, (const int32_t*)nullptr, (const int64_t*)nullptr));
+  }, 10, 200);
+  printf("%-20s reg<VB=%d,NV=%d,R=%d,L=%d,minb=%d,thr=%d> pdl=%d grid=%d: %7.2f us  %7.1f GB/s\n", label, VB, NV, R, L, MINB, threads, (int)pdl, grid,
+         ms * 1e3, (double)rows * 2 * k * es / ms / 1e6);
+}
+
 template <typename T, int NV16, int S, int NCW, int MODE>
 void run_bulk(const Shape& s, const void* in, void* out, Timer& tm, const void* ref_out = nullptr, int rpw = 0) {
   char name[128];
@@ -220,6 +251,18 @@ int main(int argc, char** argv) {
   printf("device %s, %d SMs, L2 %d MiB\n", p.name, g_sms, p.l2CacheSize >> 20);
   Timer tm;
   if (g_filter && !strcmp(g_filter, "pcie")) { pcie_study(tm); return 0; }
+  if (g_filter && !strcmp(g_filter, "small")) {
+    for (bool pdl : {false, true}) {
+      run_reg_small<float, 32, 1, 4, 1, 4, 32>("C2 64Kx768->256", 65536, 768, 256, 4, tm, pdl);
+      run_reg_small<float, 32, 1, 2, 1, 4, 32>("C2 64Kx768->256", 65536, 768, 256, 4, tm, pdl);
+      run_reg_small<float, 32, 1, 2, 1, 6, 32>("C2 64Kx768->256", 65536, 768, 256, 4, tm, pdl);
+      run_reg_small<float, 32, 1, 8, 1, 2, 32>("C2 64Kx768->256", 65536, 768, 256, 4, tm, pdl);
+      run_reg_small<float, 32, 1, 4, 1, 4, 32>("C2 64Kx768->256", 65536, 768, 256, 4, tm, pdl, 128);
+      run_reg_small<float, 32, 1, 4, 1, 4, 32>("C2 64Kx768->256", 65536, 768, 256, 4, tm, pdl, 64);
+      run_reg_small<float, 16, 2, 4, 1, 4, 32>("C2 64Kx768->256", 65536, 768, 256, 4, tm, pdl);
+    }
+    return 0;
+  }
 
   // ceilings: 4 GiB read + 4 GiB written
   {
