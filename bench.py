@@ -228,6 +228,38 @@ def quick_measure(torch, eg, wl, peak, steps=100, warmup=5):
             "frac_of_measured_peak": gbs / peak, "buffer_sets": n_sets, "steps": steps}
 
 
+def json_path_measure(eg, n=1024, D=4096, k=1024):
+    """C1 at the handler's level: the provider's response text in, the
+    handler's response text out, through etn_json_truncate_response with renormalisation on the
+    GPU — what replaces json.Decode + truncateEmbeddings + json.Encode (handlers.go:2047-2050,
+    :1891-1893, helpers.go:11-15)."""
+    import ctypes
+    from oracle import etn_oracle as oracle
+    x = oracle.fill(1, n, D, np.float64)
+    body = json.dumps({"object": "list", "data": [{"object": "embedding", "index": i, "embedding": r.tolist()} for i, r in enumerate(x)],
+                       "usage": {"prompt_tokens": 9}}).encode()
+    cap = len(body) + 2 + 26 * k * (n + 1)
+    out = ctypes.create_string_buffer(cap)
+    stats = (ctypes.c_int64 * 3)()
+    eg.init([0])
+    res = {}
+    try:
+        for label, mode in (("truncate", eg.TRUNCATE), ("truncate_renorm", eg.TRUNCATE_RENORM)):
+            best = None
+            for _ in range(4):
+                t0 = time.perf_counter()
+                w = eg.lib().etn_json_truncate_response(body, len(body), k, mode, out, cap, 1, stats)
+                dt_ = time.perf_counter() - t0
+                if w < 0:
+                    raise RuntimeError(f"packer error {w}")
+                best = dt_ if best is None else min(best, dt_)
+            res[label] = {"ms_per_response": best * 1e3, "vectors_per_s": n / best, "input_MB_per_s": len(body) / best / 1e6}
+    finally:
+        eg.shutdown()
+    res["workload"] = "%d vectors x %d float64 as JSON text (%.1f MB) -> %d dims" % (n, D, len(body) / 1e6, k)
+    return res
+
+
 def ragged_measure(torch, eg, peak, rows=1048576, D=4096, steps=50):
     """C5: ragged mixed-request batch, float64, per-request k in {64,...,1024} (seed 5), one GPU's share
     at bench scale.  Algorithmic bytes = sum over rows of 2 * k * 8."""
@@ -393,6 +425,10 @@ def run_ours(args, wl, rank, local_rank, world):
             except Exception as e:  # noqa: BLE001
                 others[name] = {"error": repr(e)[:200]}
             torch.cuda.empty_cache()
+        try:
+            others["c1_response_text"] = json_path_measure(eg)
+        except Exception as e:  # noqa: BLE001
+            others["c1_response_text"] = {"error": repr(e)[:200]}
         try:
             others["c5"] = ragged_measure(torch, eg, peak)
         except Exception as e:  # noqa: BLE001
