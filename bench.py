@@ -234,8 +234,7 @@ def json_path_measure(eg, n=1024, D=4096, k=1024):
     GPU — what replaces json.Decode + truncateEmbeddings + json.Encode (handlers.go:2047-2050,
     :1891-1893, helpers.go:11-15)."""
     import ctypes
-    from oracle import etn_oracle as oracle
-    x = oracle.fill(1, n, D, np.float64)
+    x = np.random.default_rng(1).standard_normal((n, D)) / 64.0      # synthetic response vectors
     body = json.dumps({"object": "list", "data": [{"object": "embedding", "index": i, "embedding": r.tolist()} for i, r in enumerate(x)],
                        "usage": {"prompt_tokens": 9}}).encode()
     cap = len(body) + 2 + 26 * k * (n + 1)
