@@ -4,8 +4,8 @@
 //
 //	cd baseline/go && go mod init etnbench && go test -bench . -benchmem
 //
-// BenchmarkReslice is what LLM-MCP does today: truncateEmbeddings, copied in spirit from
-// core/internal/api/handlers.go:2062-2078 (an O(1) slice-header update per vector).
+// BenchmarkReslice is what LLM-MCP does today (truncateEmbeddings,
+// core/internal/api/handlers.go:2062-2078): an O(1) slice-header update per vector.
 // BenchmarkTruncateRenorm is the loop a Go author would add for the renormalise step that
 // BASELINE.json defines; it is the loop oracle O-go models (sequential float64, no FMA at
 // GOAMD64=v1).  Shape: C1, 1,024 vectors of 4096 float64 cut to 1024.
@@ -36,21 +36,20 @@ func response() map[string]any {
 	return map[string]any{"object": "list", "data": data}
 }
 
-func truncateEmbeddings(result map[string]any, dims int) {
-	dataSlice, ok := result["data"].([]any)
-	if !ok {
-		return
-	}
-	for _, item := range dataSlice {
-		m, ok := item.(map[string]any)
-		if !ok {
-			continue
-		}
-		emb, ok := m["embedding"].([]any)
-		if ok && len(emb) > dims {
-			m["embedding"] = emb[:dims]
+// reslice restates the reference's behaviour (handlers.go:2062-2078) for the benchmark: for
+// every object in result["data"] whose "embedding" is a []any longer than dims, keep the
+// first dims entries by re-slicing; nothing else is touched.
+func reslice(result map[string]any, dims int) (cut int) {
+	items, _ := result["data"].([]any)
+	for i := range items {
+		if obj, isObj := items[i].(map[string]any); isObj {
+			if vec, isVec := obj["embedding"].([]any); isVec && len(vec) > dims {
+				obj["embedding"] = vec[:dims]
+				cut++
+			}
 		}
 	}
+	return cut
 }
 
 func BenchmarkReslice(b *testing.B) {
@@ -64,7 +63,7 @@ func BenchmarkReslice(b *testing.B) {
 		for i, it := range r["data"].([]any) { // restore, then cut
 			it.(map[string]any)["embedding"] = full[i]
 		}
-		truncateEmbeddings(r, keep)
+		reslice(r, keep)
 	}
 	b.ReportMetric(float64(batch)*float64(b.N)/b.Elapsed().Seconds(), "vectors/s")
 }
