@@ -342,3 +342,37 @@ def truncate_typed(embeddings, dims: int, renorm: bool | None = None) -> list:
         for r, i in enumerate(idx):
             out[i] = y[r].tolist()
     return out
+
+
+# ---------------------------------------------------- async job results (N4, worker side) ----
+def truncate_job_results(results: list, dims: int, renorm: bool | None = None) -> dict:
+    """Post-hoc cut of ``ollama.embed`` job results: the worker returns
+    ``{"status", "ms", "data": {"embedding": [...]}}`` per job
+    (worker/llm_worker/main.py:246-261, doc/README.md:302-307: ``result.data.embedding``), one
+    vector each, so a batch of finished jobs is packed into one host-path call per source
+    length.  Same rules as truncateEmbeddings (handlers.go:2068-2076): anything that is not a
+    list of numbers longer than ``dims`` is left alone.  Mutates ``results`` in place."""
+    stats = {"gpu_vectors": 0, "resliced_vectors": 0, "launch_groups": 0}
+    if renorm is None:
+        renorm = renorm_enabled()
+    if dims <= 0:
+        return stats
+    groups: dict[int, list[dict]] = {}
+    for res in results:
+        data = res.get("data") if isinstance(res, dict) else None
+        emb = data.get("embedding") if isinstance(data, dict) else None
+        if not isinstance(emb, list) or len(emb) <= dims:
+            continue
+        if _packable(emb):
+            groups.setdefault(len(emb), []).append(data)
+        else:
+            data["embedding"] = emb[:dims]
+            stats["resliced_vectors"] += 1
+    for D, items in groups.items():
+        x = np.array([it["embedding"] for it in items], dtype=np.float64)
+        y = truncate_norm_host(x, dims, TRUNCATE_RENORM if renorm else TRUNCATE)
+        for r, it in enumerate(items):
+            it["embedding"] = y[r].tolist()
+        stats["gpu_vectors"] += len(items)
+        stats["launch_groups"] += 1
+    return stats

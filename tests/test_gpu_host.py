@@ -225,3 +225,22 @@ def test_host_path_concurrent_handlers(oracle):
     [t.start() for t in th]
     [t.join() for t in th]
     assert not errs, errs
+
+
+def test_job_results_async_path(oracle):
+    """worker/llm_worker/main.py:246-261: one vector per finished ollama.embed job."""
+    x = oracle.fill(14, 6, 768, np.float64)
+    jobs = [{"status": 200, "ms": 12, "data": {"embedding": r.tolist()}} for r in x]
+    jobs[1]["data"]["embedding"] = jobs[1]["data"]["embedding"][:64]
+    jobs += [{"status": 500, "ms": 3, "data": {}}, {"status": 200, "ms": 1, "data": {"embedding": None}}, "junk"]
+    keep = copy.deepcopy(jobs)
+    st = eg.truncate_job_results(jobs, 256, renorm=True)
+    assert st == {"gpu_vectors": 5, "resliced_vectors": 0, "launch_groups": 1}
+    for j, k0 in zip(jobs[:6], keep[:6]):
+        e0 = k0["data"]["embedding"]
+        if len(e0) > 256:
+            _ulp(oracle, np.array(j["data"]["embedding"]), oracle.renorm_exact(np.array([e0]), 256)[0])
+        else:
+            assert j == k0
+    assert jobs[6:] == keep[6:]
+    assert eg.truncate_job_results(copy.deepcopy(keep), 0)["gpu_vectors"] == 0
