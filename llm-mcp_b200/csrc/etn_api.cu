@@ -100,14 +100,13 @@ int launch_kernel(void (*kern)(KArgs...), int grid, cudaStream_t s, Args... args
 }
 
 // MINB = resident blocks per SM the register allocation is held to.
-template <typename T, int VB, int NV, int R, int L, int MODE, int MINB, bool RAGGED>
-int launch_reg(const void* in, void* out, int64_t batch, int64_t in_pitch, int nvec, int64_t D,
-               const int32_t* k_per_row, const int64_t* out_offsets, int waves, cudaStream_t s) {
-  auto kern = rows_reg_kernel<T, VB, NV, R, L, MODE, MINB, VB == 32 ? 1 : 0, RAGGED>;
+template <typename T, int VB, int NV, int R, int L, int MODE, int MINB>
+int launch_reg(const void* in, void* out, int64_t batch, int64_t in_pitch, int nvec, int waves, cudaStream_t s) {
+  auto kern = rows_reg_kernel<T, VB, NV, R, L, MODE, MINB, VB == 32 ? 1 : 0>;
   int grid = 0;
   const int64_t rows_per_block = (int64_t)kWarpsPerBlock * R * (32 / L);
   if (int rc = grid_for(kern, (batch + rows_per_block - 1) / rows_per_block, waves, &grid)) return rc;
-  return launch_kernel(kern, grid, s, (const char*)in, (char*)out, batch, in_pitch, nvec, D, k_per_row, out_offsets);
+  return launch_kernel(kern, grid, s, (const char*)in, (char*)out, batch, in_pitch, nvec);
 }
 
 // Wide rows: one row per block iteration, double-buffered in shared memory.
@@ -149,12 +148,11 @@ int launch_wide(const void* in, void* out, int64_t batch, int64_t in_pitch, int 
 
 // Bulk-async (TMA) ring kernel: 4 warps per block, each with its own S-slot ring of row
 // prefixes in shared memory; every warp owns `rpw` consecutive rows.
-template <typename T, int NV16, int S, int MODE, bool RAGGED>
-int launch_bulk(const void* in, void* out, int64_t batch, int64_t in_pitch, int nvec16, int rpw,
-                int64_t D, const int32_t* k_per_row, const int64_t* out_offsets, cudaStream_t s) {
+template <typename T, int NV16, int S, int MODE>
+int launch_bulk(const void* in, void* out, int64_t batch, int64_t in_pitch, int nvec16, int rpw, cudaStream_t s) {
   constexpr int NCW = 4;
   constexpr size_t smem = (size_t)NCW * S * NV16 * 512 + (size_t)NCW * S * 8;
-  auto kern = rows_bulk_kernel<T, NV16, S, NCW, MODE, RAGGED>;
+  auto kern = rows_bulk_kernel<T, NV16, S, NCW, MODE>;
   if (smem > 48 * 1024) {                              // opt in to large dynamic shared memory once per device
     static std::atomic<uint64_t> done{0};
     int dev = 0;
@@ -184,8 +182,7 @@ int launch_bulk(const void* in, void* out, int64_t batch, int64_t in_pitch, int 
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
-  return counted_launch(cudaLaunchKernelEx(&cfg, kern, (const char*)in, (char*)out, batch, in_pitch, nvec16, rpw,
-                                           D, k_per_row, out_offsets));
+  return counted_launch(cudaLaunchKernelEx(&cfg, kern, (const char*)in, (char*)out, batch, in_pitch, nvec16, rpw));
 }
 
 template <typename T, int MODE>
@@ -228,11 +225,11 @@ int launch_dense(const void* in, void* out, int64_t batch, int64_t D, int64_t kk
         k_bytes > 512 && k_bytes <= 8192) {
       const int nvec16 = (int)(k_bytes / 16);
       const int nv = (nvec16 + 31) / 32;
-      if (nv <= 2)  return launch_bulk<T, 2, 4, MODE, false>(in, out, batch, in_pitch, nvec16, 8, D, nullptr, nullptr, s);
-      if (nv <= 4)  return launch_bulk<T, 4, 2, MODE, false>(in, out, batch, in_pitch, nvec16, 8, D, nullptr, nullptr, s);
-      if (nv <= 8)  return launch_bulk<T, 8, 2, MODE, false>(in, out, batch, in_pitch, nvec16, 4, D, nullptr, nullptr, s);
-      if (nv <= 12) return launch_bulk<T, 12, 2, MODE, false>(in, out, batch, in_pitch, nvec16, 4, D, nullptr, nullptr, s);
-      return launch_bulk<T, 16, 2, MODE, false>(in, out, batch, in_pitch, nvec16, 4, D, nullptr, nullptr, s);
+      if (nv <= 2)  return launch_bulk<T, 2, 4, MODE>(in, out, batch, in_pitch, nvec16, 8, s);
+      if (nv <= 4)  return launch_bulk<T, 4, 2, MODE>(in, out, batch, in_pitch, nvec16, 8, s);
+      if (nv <= 8)  return launch_bulk<T, 8, 2, MODE>(in, out, batch, in_pitch, nvec16, 4, s);
+      if (nv <= 12) return launch_bulk<T, 12, 2, MODE>(in, out, batch, in_pitch, nvec16, 4, s);
+      return launch_bulk<T, 16, 2, MODE>(in, out, batch, in_pitch, nvec16, 4, s);
     }
   }
   const bool tile16 = aligned_to(in, 16) && aligned_to(out, 16) && in_pitch % 16 == 0 && k_bytes % 16 == 0;
@@ -244,27 +241,27 @@ int launch_dense(const void* in, void* out, int64_t batch, int64_t D, int64_t kk
     const int nv = (nvec + 31) / 32;
     // short rows: 8 or 16 lanes per row, so a warp finishes 4 or 2 rows per reduction
     constexpr int RS = heavy ? 2 : 8, MBS = heavy ? 4 : 2;
-    if (nvec <= 8)  return launch_reg<TT, 32, 1, RS, 8, MODE, MBS, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
-    if (nvec <= 16) return launch_reg<TT, 32, 1, RS, 16, MODE, MBS, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
-    if (nv <= 1) return launch_reg<TT, 32, 1, R1, 32, MODE, MB, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
-    if (nv <= 2) return launch_reg<TT, 32, 2, R2, 32, MODE, MB, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
-    if (nv <= 4) return launch_reg<TT, 32, 4, 1, 32, MODE, MB4, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
+    if (nvec <= 8)  return launch_reg<TT, 32, 1, RS, 8, MODE, MBS>(in, out, batch, in_pitch, nvec, W, s);
+    if (nvec <= 16) return launch_reg<TT, 32, 1, RS, 16, MODE, MBS>(in, out, batch, in_pitch, nvec, W, s);
+    if (nv <= 1) return launch_reg<TT, 32, 1, R1, 32, MODE, MB>(in, out, batch, in_pitch, nvec, W, s);
+    if (nv <= 2) return launch_reg<TT, 32, 2, R2, 32, MODE, MB>(in, out, batch, in_pitch, nvec, W, s);
+    if (nv <= 4) return launch_reg<TT, 32, 4, 1, 32, MODE, MB4>(in, out, batch, in_pitch, nvec, W, s);
     // 4-8 KiB rows: float32 renorm does as well through the bulk ring (6.79 vs 6.65 TB/s)
     if constexpr (MODE == kModeRenorm && !heavy)
-      return launch_bulk<T, 16, 2, MODE, false>(in, out, batch, in_pitch, (int)(k_bytes / 16), 4, D, nullptr, nullptr, s);
-    return launch_reg<TT, 32, 8, 1, 32, MODE, MB8, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
+      return launch_bulk<T, 16, 2, MODE>(in, out, batch, in_pitch, (int)(k_bytes / 16), 4, s);
+    return launch_reg<TT, 32, 8, 1, 32, MODE, MB8>(in, out, batch, in_pitch, nvec, W, s);
   }
   if (aligned_to(in, 16) && aligned_to(out, 16) && in_pitch % 16 == 0 && k_bytes % 16 == 0 &&
       k_bytes <= 16 * 512) {
     const int nvec = (int)(k_bytes / 16);
     const int nv = (nvec + 31) / 32;
-    if (nvec <= 8)  return launch_reg<TT, 16, 1, 2 * R1, 8, MODE, MB, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
-    if (nvec <= 16) return launch_reg<TT, 16, 1, 2 * R1, 16, MODE, MB, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
-    if (nv <= 1) return launch_reg<TT, 16, 1, 2 * R1, 32, MODE, MB, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
-    if (nv <= 2) return launch_reg<TT, 16, 2, R1, 32, MODE, MB, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
-    if (nv <= 4) return launch_reg<TT, 16, 4, R2, 32, MODE, MB, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
-    if (nv <= 8) return launch_reg<TT, 16, 8, 1, 32, MODE, MB4, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
-    return launch_reg<TT, 16, 16, 1, 32, MODE, MB8, false>(in, out, batch, in_pitch, nvec, D, nullptr, nullptr, W, s);
+    if (nvec <= 8)  return launch_reg<TT, 16, 1, 2 * R1, 8, MODE, MB>(in, out, batch, in_pitch, nvec, W, s);
+    if (nvec <= 16) return launch_reg<TT, 16, 1, 2 * R1, 16, MODE, MB>(in, out, batch, in_pitch, nvec, W, s);
+    if (nv <= 1) return launch_reg<TT, 16, 1, 2 * R1, 32, MODE, MB>(in, out, batch, in_pitch, nvec, W, s);
+    if (nv <= 2) return launch_reg<TT, 16, 2, R1, 32, MODE, MB>(in, out, batch, in_pitch, nvec, W, s);
+    if (nv <= 4) return launch_reg<TT, 16, 4, R2, 32, MODE, MB>(in, out, batch, in_pitch, nvec, W, s);
+    if (nv <= 8) return launch_reg<TT, 16, 8, 1, 32, MODE, MB4>(in, out, batch, in_pitch, nvec, W, s);
+    return launch_reg<TT, 16, 16, 1, 32, MODE, MB8>(in, out, batch, in_pitch, nvec, W, s);
   }
   // prefix not 16-byte tileable (odd k) but 16-byte aligned input rows: staged through the ring
   if (aligned_to(in, 16) && in_pitch % 16 == 0 && k_bytes <= 8192 - 16)

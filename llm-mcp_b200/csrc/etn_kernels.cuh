@@ -341,16 +341,10 @@ __device__ __forceinline__ void general_row(const T* __restrict__ x, T* __restri
 // before anything is consumed (R*NV*VB*32 bytes per warp in flight).  Requires VB-aligned
 // rows on both sides; nvec = VB-byte vectors per prefix (<= NV*L).  L < 32 keeps short rows
 // (<= 512 B) from paying a whole warp's reduction and scale computation each.
-//
-// RAGGED (L = 32, R = 1): row r keeps k_per_row[r] elements, written at element offset
-// out_offsets[r].  Rows whose prefix is not VB-tileable, or longer than the registers hold,
-// take general_row.
-template <typename T, int VB, int NV, int R, int L, int MODE, int MINB, int HINT, bool RAGGED>
+template <typename T, int VB, int NV, int R, int L, int MODE, int MINB, int HINT>
 __global__ void __launch_bounds__(kThreads, MINB)
 rows_reg_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t batch,
-                int64_t in_pitch /*bytes*/, int nvec_dense, int64_t D,
-                const int32_t* __restrict__ k_per_row, const int64_t* __restrict__ out_offsets) {
-  static_assert(!RAGGED || (L == 32 && R == 1), "ragged rows are one per warp");
+                int64_t in_pitch /*bytes*/, int nvec_dense) {
   pdl_prologue();
   constexpr int W = VB / 4, NW = NV * W;
   constexpr int S = 32 / L;                            // rows side by side in a warp
@@ -370,22 +364,6 @@ rows_reg_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t bat
       const char* src = in + row * in_pitch;
       nvec[r] = row_ok ? nvec_dense : 0;
       dst[r] = out + row * ((int64_t)nvec_dense * VB);
-      if constexpr (RAGGED) {
-        if (row_ok) {
-          int64_t kr = k_per_row[row];
-          if (kr > D) kr = D;
-          const int64_t kb = kr * (int64_t)sizeof(T);
-          dst[r] = out + out_offsets[row] * (int64_t)sizeof(T);
-          const bool tile = (kb % VB == 0) && (kb <= (int64_t)NV * 32 * VB) &&
-                            ((reinterpret_cast<uintptr_t>(dst[r]) % VB) == 0);
-          if (tile) {
-            nvec[r] = (int)(kb / VB);
-          } else {                                     // warp-uniform: odd row, slow path
-            nvec[r] = 0;
-            general_row<T, MODE>((const T*)src, (T*)dst[r], kr, lane);
-          }
-        }
-      }
 #pragma unroll
       for (int j = 0; j < NV; ++j) {
         const int idx = j * L + sl;
@@ -470,13 +448,10 @@ __device__ __forceinline__ void bulk_load_row(uint32_t dst, const void* src, uin
                :: "r"(dst), "l"(src), "r"(bytes), "r"(bar), "l"(policy) : "memory");
 }
 
-// RAGGED: row r keeps k_per_row[r] elements at element offset out_offsets[r]; a row that is
-// not 16-byte tileable or does not fit a slot is not staged and takes general_row instead.
-template <typename T, int NV16, int S, int NCW, int MODE, bool RAGGED>
+template <typename T, int NV16, int S, int NCW, int MODE>
 __global__ void __launch_bounds__(NCW * 32, (NV16 > 12 ? ((sizeof(T) == 4 && MODE == kModeRenorm) ? 2 : 3) : 4))
 rows_bulk_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t batch,
-                 int64_t in_pitch /*bytes*/, int nvec16_dense, int rows_per_warp, int64_t D,
-                 const int32_t* __restrict__ k_per_row, const int64_t* __restrict__ out_offsets) {
+                 int64_t in_pitch /*bytes*/, int nvec16, int rows_per_warp) {
   constexpr int NW = NV16 * 4;
   constexpr int SLOT = NV16 * 32 * 16;                 // bytes per ring slot
   extern __shared__ __align__(128) unsigned char ring[];
@@ -495,21 +470,7 @@ rows_bulk_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t ba
   __syncthreads();
   pdl_prologue();
 
-  // Bytes of row `row` to stage (0: the row goes through general_row) and where it lands.
-  auto row_plan = [&](int64_t row, char*& dst) -> uint32_t {
-    if constexpr (!RAGGED) {
-      dst = out + row * ((int64_t)nvec16_dense * 16);
-      return (uint32_t)nvec16_dense * 16u;
-    } else {
-      int64_t kr = k_per_row[row];
-      if (kr > D) kr = D;
-      const int64_t kb = kr * (int64_t)sizeof(T);
-      dst = out + out_offsets[row] * (int64_t)sizeof(T);
-      const bool tile = kb > 0 && (kb % 16 == 0) && kb <= (int64_t)SLOT &&
-                        (reinterpret_cast<uintptr_t>(dst) % 16) == 0;
-      return tile ? (uint32_t)kb : 0u;
-    }
-  };
+  const uint32_t row_bytes = (uint32_t)nvec16 * 16u;
 
   uint64_t policy;
   asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
@@ -524,37 +485,14 @@ rows_bulk_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t ba
 #pragma unroll
     for (int s = 0; s < S; ++s) {
       const int64_t row = gw + s * tw;
-      if (row < batch) {
-        char* d;
-        const uint32_t nb = row_plan(row, d);
-        if (nb) bulk_load_row(smem_u32(my_slots + s * SLOT), in + row * in_pitch, nb, bar0 + 8u * s, policy);
-      }
+      if (row < batch) bulk_load_row(smem_u32(my_slots + s * SLOT), in + row * in_pitch, row_bytes, bar0 + 8u * s, policy);
     }
   }
   int s = 0;
-  uint32_t parity = 0;                                  // per-slot phase, kept as a bit mask
+  uint32_t parity = 0;
   for (int64_t row = gw; row < batch; row += tw) {
-    char* dst;
-    const uint32_t row_bytes = row_plan(row, dst);
     const unsigned char* slot = my_slots + s * SLOT;
-    const int64_t next = row + (int64_t)S * tw;
-    if constexpr (RAGGED) {
-      if (row_bytes == 0) {                             // warp-uniform: odd row, nothing was staged
-        if (lane == 0 && next < batch) {
-          char* d;
-          const uint32_t nb = row_plan(next, d);
-          if (nb) bulk_load_row(smem_u32(slot), in + next * in_pitch, nb, bar0 + 8u * s, policy);
-        }
-        int64_t kr = k_per_row[row];
-        if (kr > D) kr = D;
-        general_row<T, MODE>((const T*)(in + row * in_pitch), (T*)dst, kr, lane);
-        if (++s == S) s = 0;
-        continue;
-      }
-    }
-    mbar_wait(bar0 + 8u * s, (parity >> s) & 1u);
-    parity ^= 1u << s;
-    const int nvec16 = (int)(row_bytes >> 4);
+    mbar_wait(bar0 + 8u * s, parity);
     uint32_t w[NW];
 #pragma unroll
     for (int j = 0; j < NV16; ++j) {
@@ -567,27 +505,26 @@ rows_bulk_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t ba
       }
     }
     __syncwarp();                                       // every lane has its copy: slot is free
-    if (lane == 0 && next < batch) {
-      char* d;
-      const uint32_t nb = row_plan(next, d);
-      if (nb) bulk_load_row(smem_u32(slot), in + next * in_pitch, nb, bar0 + 8u * s, policy);
-    }
+    const int64_t next = row + (int64_t)S * tw;
+    if (lane == 0 && next < batch)
+      bulk_load_row(smem_u32(slot), in + next * in_pitch, row_bytes, bar0 + 8u * s, policy);
+
     if constexpr (MODE == kModeRenorm) {
-      const int used = RAGGED ? 4 * ((nvec16 + 31) >> 5) : NW;   // words per lane that can be non-zero
       if constexpr (sizeof(T) == 4) {
-        Scale32 sc; sc.from_ss(warp_sum(lane_sumsq32<NW>(w, used)));
-        lane_apply32<NW>(w, sc, used);
+        Scale32 sc; sc.from_ss(warp_sum(lane_sumsq32<NW>(w)));
+        lane_apply32<NW>(w, sc);
       } else {
-        const Scale64 sc = row_scale64<NW, 32>(w, used);
-        lane_apply64<NW>(w, sc, used);
+        const Scale64 sc = row_scale64<NW, 32>(w);
+        lane_apply64<NW>(w, sc);
       }
     }
+    char* dst = out + row * (int64_t)row_bytes;
 #pragma unroll
     for (int j = 0; j < NV16; ++j) {
       const int idx = j * 32 + lane;
       if (idx < nvec16) st_vec<16, 0>(dst + (int64_t)idx * 16, &w[j * 4]);
     }
-    if (++s == S) s = 0;
+    if (++s == S) { s = 0; parity ^= 1u; }
   }
 }
 

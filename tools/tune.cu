@@ -51,7 +51,7 @@ void run_reg(const Shape& s, const void* in, void* out, Timer& tm, int waves = 1
   char name[128];
   snprintf(name, sizeof name, "%s reg<VB=%d,NV=%d,R=%d,L=%d,mode=%d,minb=%d,hint=%d,w=%d>", s.name, VB, NV, R, L, MODE, MINB, HINT, waves);
   if (!want(name)) return;
-  auto kern = rows_reg_kernel<T, VB, NV, R, L, MODE, MINB, HINT, false>;
+  auto kern = rows_reg_kernel<T, VB, NV, R, L, MODE, MINB, HINT>;
   int per_sm = 0;
   CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kThreads, 0));
   cudaFuncAttributes fa; CK(cudaFuncGetAttributes(&fa, kern));
@@ -59,7 +59,7 @@ void run_reg(const Shape& s, const void* in, void* out, Timer& tm, int waves = 1
   const int64_t need = (s.rows + rpb - 1) / rpb;
   const int grid = waves > 0 ? (int)std::min<int64_t>(need, (int64_t)g_sms * per_sm * waves) : (int)need;
   const int nvec = (int)(s.k * s.es / VB);
-  double ms = tm.ms([&](int) { kern<<<grid, kThreads>>>((const char*)in, (char*)out, s.rows, s.D * s.es, nvec, s.D, nullptr, nullptr); }, 3, g_iters);
+  double ms = tm.ms([&](int) { kern<<<grid, kThreads>>>((const char*)in, (char*)out, s.rows, s.D * s.es, nvec); }, 3, g_iters);
   CK(cudaGetLastError());
   double gbs = (double)s.rows * 2 * s.k * s.es / ms / 1e6;
   printf("%-78s %8.3f ms %8.1f GB/s  regs=%d occ=%d grid=%d\n", name, ms, gbs, fa.numRegs, per_sm, grid);
@@ -79,7 +79,7 @@ void run_reg_small(const char* label, int64_t rows, int64_t D, int64_t k, int es
     }
     have = rows * D;
   }
-  auto kern = rows_reg_kernel<T, VB, NV, R, L, MODE, MINB, 1, false>;
+  auto kern = rows_reg_kernel<T, VB, NV, R, L, MODE, MINB, 1>;
   const int64_t rpb = (threads / 32) * R * (32 / L);
   const int grid = (int)((rows + rpb - 1) / rpb);
   const int nvec = (int)(k * es / VB);
@@ -90,7 +90,7 @@ void run_reg_small(const char* label, int64_t rows, int64_t D, int64_t k, int es
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
   double ms = tm.ms([&](int i) {
-    CK(cudaLaunchKernelEx(&cfg, kern, (const char*)in[i % NSET], (char*)out[i % NSET], rows, D * es, nvec, D, (const int32_t*)nullptr, (const int64_t*)nullptr));
+    CK(cudaLaunchKernelEx(&cfg, kern, (const char*)in[i % NSET], (char*)out[i % NSET], rows, D * es, nvec));
   }, 10, 200);
   printf("%-20s reg<VB=%d,NV=%d,R=%d,L=%d,minb=%d,thr=%d> pdl=%d grid=%d: %7.2f us  %7.1f GB/s\n", label, VB, NV, R, L, MINB, threads, (int)pdl, grid,
          ms * 1e3, (double)rows * 2 * k * es / ms / 1e6);
@@ -101,7 +101,7 @@ void run_bulk(const Shape& s, const void* in, void* out, Timer& tm, const void* 
   char name[128];
   snprintf(name, sizeof name, "%s bulk<NV16=%d,S=%d,NCW=%d,mode=%d,rpw=%d>", s.name, NV16, S, NCW, MODE, rpw);
   if (!want(name)) return;
-  auto kern = rows_bulk_kernel<T, NV16, S, NCW, MODE, false>;
+  auto kern = rows_bulk_kernel<T, NV16, S, NCW, MODE>;
   const size_t smem = (size_t)NCW * S * NV16 * 512 + (size_t)NCW * S * 8;
   CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   cudaFuncAttributes fa; CK(cudaFuncGetAttributes(&fa, kern));
@@ -109,7 +109,7 @@ void run_bulk(const Shape& s, const void* in, void* out, Timer& tm, const void* 
   const size_t out_bytes = (size_t)s.rows * s.k * s.es;
   const int grid = rpw > 0 ? (int)((s.rows + (int64_t)NCW * rpw - 1) / ((int64_t)NCW * rpw)) : g_sms;
   CK(cudaMemset(out, 0, out_bytes));
-  double ms = tm.ms([&](int) { kern<<<grid, NCW * 32, smem>>>((const char*)in, (char*)out, s.rows, s.D * s.es, nvec16, rpw, s.D, nullptr, nullptr); }, 3, g_iters);
+  double ms = tm.ms([&](int) { kern<<<grid, NCW * 32, smem>>>((const char*)in, (char*)out, s.rows, s.D * s.es, nvec16, rpw); }, 3, g_iters);
   CK(cudaGetLastError());
   double gbs = (double)s.rows * 2 * s.k * s.es / ms / 1e6;
   int same = -1;
@@ -186,36 +186,36 @@ static void pcie_study(Timer& tm) {
     rep("pcie H2D + D2H concurrently (each direction)", t / 5, pre_bytes);
   }
   const int nvec = (int)(k * es / 32);
-  auto kern = rows_reg_kernel<float, 32, 4, 1, 32, 1, 4, 1, false>;
+  auto kern = rows_reg_kernel<float, 32, 4, 1, 32, 1, 4, 1>;
   const int grid = (int)((rows + 7) / 8);
-  ms = tm.ms([&](int) { kern<<<grid, kThreads>>>(hin, hout, rows, D * es, nvec, D, nullptr, nullptr); }, 1, 5);
+  ms = tm.ms([&](int) { kern<<<grid, kThreads>>>(hin, hout, rows, D * es, nvec); }, 1, 5);
   rep("zero-copy kernel: host in -> host out (per direction)", ms, pre_bytes);
-  ms = tm.ms([&](int) { kern<<<grid, kThreads>>>(hin, dout, rows, D * es, nvec, D, nullptr, nullptr); }, 1, 5);
+  ms = tm.ms([&](int) { kern<<<grid, kThreads>>>(hin, dout, rows, D * es, nvec); }, 1, 5);
   rep("zero-copy kernel: host in -> device out", ms, pre_bytes);
-  ms = tm.ms([&](int) { kern<<<grid, kThreads>>>(din, hout, rows, D * es, nvec, D, nullptr, nullptr); }, 1, 5);
+  ms = tm.ms([&](int) { kern<<<grid, kThreads>>>(din, hout, rows, D * es, nvec); }, 1, 5);
   rep("zero-copy kernel: device in -> host out", ms, pre_bytes);
-  auto kern16 = rows_reg_kernel<float, 16, 8, 1, 32, 1, 4, 0, false>;
-  ms = tm.ms([&](int) { kern16<<<grid, kThreads>>>(hin, hout, rows, D * es, (int)(k * es / 16), D, nullptr, nullptr); }, 1, 5);
+  auto kern16 = rows_reg_kernel<float, 16, 8, 1, 32, 1, 4, 0>;
+  ms = tm.ms([&](int) { kern16<<<grid, kThreads>>>(hin, hout, rows, D * es, (int)(k * es / 16)); }, 1, 5);
   rep("zero-copy kernel 128-bit: host in -> host out", ms, pre_bytes);
   for (int g : {148, 296, 592, 2368}) {
     char nm[96]; snprintf(nm, sizeof nm, "zero-copy kernel grid=%d: host in -> host out", g);
-    ms = tm.ms([&](int) { kern<<<g, kThreads>>>(hin, hout, rows, D * es, nvec, D, nullptr, nullptr); }, 1, 5);
+    ms = tm.ms([&](int) { kern<<<g, kThreads>>>(hin, hout, rows, D * es, nvec); }, 1, 5);
     rep(nm, ms, pre_bytes);
   }
   // small request latency: C1 1024 x 4096 f64 -> 1024 (8 MiB each way)
   {
-    auto k64 = rows_reg_kernel<double, 32, 8, 1, 32, 1, 2, 1, false>;
-    ms = tm.ms([&](int) { k64<<<128, kThreads>>>(hin, hout, 1024, 4096 * 8, 256, 4096, nullptr, nullptr); }, 2, 20);
+    auto k64 = rows_reg_kernel<double, 32, 8, 1, 32, 1, 2, 1>;
+    ms = tm.ms([&](int) { k64<<<128, kThreads>>>(hin, hout, 1024, 4096 * 8, 256); }, 2, 20);
     rep("C1 zero-copy kernel host->host (8 MiB each way)", ms, 8.0 * 1048576);
     ms = tm.ms([&](int) {
       CK(cudaMemcpy2DAsync(din, 8192, hin, 32768, 8192, 1024, cudaMemcpyHostToDevice));
-      k64<<<128, kThreads>>>(din, dout, 1024, 8192, 256, 1024, nullptr, nullptr);
+      k64<<<128, kThreads>>>(din, dout, 1024, 8192, 256);
       CK(cudaMemcpyAsync(hout, dout, 8388608, cudaMemcpyDeviceToHost)); }, 2, 20);
     rep("C1 staged H2D(2-D) + kernel + D2H (8 MiB each way)", ms, 8.0 * 1048576);
   }
   // C1 through chunked pipelines: wall-clock per call, n chunks round-robin over 4 streams
   {
-    auto k64 = rows_reg_kernel<double, 32, 8, 1, 32, 1, 2, 1, false>;
+    auto k64 = rows_reg_kernel<double, 32, 8, 1, 32, 1, 2, 1>;
     cudaStream_t st[4];
     for (auto& x : st) CK(cudaStreamCreateWithFlags(&x, cudaStreamNonBlocking));
     for (int nch : {1, 2, 4, 8}) {
@@ -227,7 +227,7 @@ static void pcie_study(Timer& tm) {
             char* d = din + (size_t)c * rows_c * 8192;
             if (twod) CK(cudaMemcpy2DAsync(d, 8192, hin + (size_t)c * rows_c * 32768, 32768, 8192, rows_c, cudaMemcpyHostToDevice, s));
             else CK(cudaMemcpyAsync(d, hin + (size_t)c * rows_c * 8192, (size_t)rows_c * 8192, cudaMemcpyHostToDevice, s));
-            k64<<<(rows_c + 7) / 8, kThreads, 0, s>>>(d, d, rows_c, 8192, 256, 1024, nullptr, nullptr);
+            k64<<<(rows_c + 7) / 8, kThreads, 0, s>>>(d, d, rows_c, 8192, 256);
             CK(cudaMemcpyAsync(hout + (size_t)c * rows_c * 8192, d, (size_t)rows_c * 8192, cudaMemcpyDeviceToHost, s));
           }
           for (auto& x : st) CK(cudaStreamSynchronize(x));
