@@ -320,3 +320,27 @@ def test_full_size_properties(oracle, name, rows, D, k, dt, seed):
     assert (y2 - y).abs().max().item() <= np.finfo(dt).eps
     del y, y2
     torch.cuda.empty_cache()
+
+
+def test_cuda_graph_capture_and_replay(oracle):
+    """Request-sized launches are launch-latency-bound; the device entry points only enqueue
+    kernels on the caller's stream, so a caller can capture a burst of them in a CUDA graph."""
+    xs = [gu.dev_fill(50 + i, 2048, 1024, np.float32) for i in range(4)]
+    ys = [torch.empty((2048, 256), dtype=torch.float32, device="cuda") for _ in range(4)]
+    for x, y in zip(xs, ys):                               # warm up outside the capture
+        gu.run_dense(x, 256, eg.TRUNCATE_RENORM, out=y)
+    torch.cuda.synchronize()
+    want = [y.clone() for y in ys]
+    for y in ys:
+        y.zero_()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for x, y in zip(xs, ys):
+            gu.run_dense(x, 256, eg.TRUNCATE_RENORM, out=y)
+    for _ in range(3):
+        g.replay()
+    torch.cuda.synchronize()
+    for y, w in zip(ys, want):
+        assert torch.equal(y, w)
+    d, _ = oracle.max_ulp(ys[0].cpu().numpy(), oracle.renorm_exact(xs[0].cpu().numpy(), 256))
+    assert 0 <= d <= ULP_DOC

@@ -57,3 +57,32 @@ for rows_, D_, k_, dt_ in ((1024, 4096, 1024, np.float64), (64, 4096, 1024, np.f
     del hx, hy
     pin_in.free(); pin_out.free()
 eg.shutdown()
+
+# C2 and C1 replayed from a CUDA graph of 24 launches over rotating buffers
+for name in ("c2", "c1"):
+    wl = bench.WORKLOADS[name]
+    dt = bench.NPDT[wl["dtype"]]; tdt = torch.float32 if wl["dtype"] == "f32" else torch.float64
+    es = np.dtype(dt).itemsize; rows_, D_, k_, code = wl["rows"], wl["D"], wl["k"], eg.dtype_code(dt)
+    nset = max(6, -(-4 * bench.L2_BYTES // (rows_ * 2 * k_ * es)))
+    xs = [torch.empty((rows_, D_), dtype=tdt, device="cuda") for _ in range(nset)]
+    ys = [torch.empty((rows_, k_), dtype=tdt, device="cuda") for _ in range(nset)]
+    for i, x in enumerate(xs):
+        eg.check(L.etn_fill_synthetic(3 + i, 0, rows_, D_, D_, D_, code, x.data_ptr(), torch.cuda.current_stream().cuda_stream), "fill")
+    eg.check(L.embed_truncate_norm(rows_, D_, k_, code, xs[0].data_ptr(), ys[0].data_ptr(), torch.cuda.current_stream().cuda_stream), "warm")
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        s_ = torch.cuda.current_stream().cuda_stream
+        for i in range(24):
+            eg.check(L.embed_truncate_norm(rows_, D_, k_, code, xs[i % nset].data_ptr(), ys[i % nset].data_ptr(), s_), "cap")
+    for _ in range(3):
+        g.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(20):
+        g.replay()
+    e1.record(); torch.cuda.synchronize()
+    t = e0.elapsed_time(e1) * 1e-3 / (20 * 24)
+    print("graph replay %s: %.2f us per launch  %.0f GB/s" % (name, t * 1e6, rows_ * 2 * k_ * es / t / 1e9), flush=True)
+    del xs, ys
