@@ -280,9 +280,9 @@ __device__ __forceinline__ Scale64 row_scale64(const uint32_t (&w)[NW], int used
 // ------------------------------------------------------ one row, one warp, any shape ----
 // Two passes over the row prefix with element-wise coalesced accesses; the second pass hits
 // L1/L2.  Used by rows_general_kernel and as the per-row fallback of the ragged path.
+// (x and y may be the same row when the caller normalises in place, so no __restrict__.)
 template <typename T, int MODE>
-__device__ __forceinline__ void general_row(const T* __restrict__ x, T* __restrict__ y, int64_t kr,
-                                            int lane) {
+__device__ __forceinline__ void general_row(const T* x, T* y, int64_t kr, int lane) {
   if constexpr (MODE == kModeTruncate) {
     for (int64_t i = lane; i < kr; i += 32) y[i] = x[i];
   } else if constexpr (sizeof(T) == 4) {
@@ -917,7 +917,7 @@ rows_wide_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t ba
 // out_offsets == nullptr -> dense output.
 template <typename T, int MODE>
 __global__ void __launch_bounds__(kThreads)
-rows_general_kernel(const T* __restrict__ in, T* __restrict__ out, int64_t batch, int64_t D,
+rows_general_kernel(const T* in, T* out, int64_t batch, int64_t D,
                     int64_t k, const int32_t* __restrict__ k_per_row,
                     const int64_t* __restrict__ out_offsets) {
   pdl_prologue();

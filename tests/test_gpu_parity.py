@@ -175,11 +175,14 @@ def test_unaligned_pointers(oracle, dt):
 
 
 def test_in_place_full_rows(oracle):
+    """out == in with k >= D, on every kernel family: registers, bulk ring, wide rows, page
+    ring (odd k) and the general kernel (odd D)."""
     for dt in (np.float32, np.float64):
-        xh = oracle.fill(15, 1000, 1024, dt)
-        x = gu.to_dev(xh)
-        gu.run_dense(x, 1024, eg.TRUNCATE_RENORM, out=x)
-        assert_ulp(oracle, x.cpu().numpy(), oracle.renorm_exact(xh, 1024), what="in place")
+        for rows, D in ((1000, 1024), (1000, 96), (300, 4096), (300, 1001), (300, 1003 if dt == np.float32 else 1001), (64, 9000)):
+            xh = oracle.fill(15, rows, D, dt)
+            x = gu.to_dev(xh)
+            gu.run_dense(x, D, eg.TRUNCATE_RENORM, out=x)
+            assert_ulp(oracle, x.cpu().numpy(), oracle.renorm_exact(xh, D), what=f"in place {rows}x{D}")
 
 
 def test_ragged_against_oracle(oracle):
