@@ -203,7 +203,7 @@ int launch_ring(const void* in, void* out, int64_t batch, int64_t D, int64_t k_d
 //   16-byte tileable, 8 KiB - 112 KiB:                rows_wide (row in shared memory, whole block)
 //   32-byte tileable, <= 8 KiB:                       rows_reg with 256-bit accesses
 //   16-byte tileable, <= 8 KiB:                       rows_reg with 128-bit accesses
-//   odd k or odd D, <= 8 KiB:                         rows_ring (aligned span staged, element-wise)
+//   16-byte aligned input rows, odd k, <= 8 KiB:      rows_ring (staged rounded up, element-wise)
 //   anything else:                                    rows_general
 // Truncation moves bytes, so one instantiation (T = float) serves both element types.
 template <typename T, int MODE>
@@ -263,8 +263,8 @@ int launch_dense(const void* in, void* out, int64_t batch, int64_t D, int64_t kk
     if (nv <= 8) return launch_reg<TT, 16, 8, 1, 32, MODE, MB4>(in, out, batch, in_pitch, nvec, W, s);
     return launch_reg<TT, 16, 16, 1, 32, MODE, MB8>(in, out, batch, in_pitch, nvec, W, s);
   }
-  // prefix not 16-byte tileable (odd k) or rows off the 16-byte grid (odd D): staged through the ring
-  if (k_bytes <= 8192 - 32)
+  // prefix not 16-byte tileable (odd k) but 16-byte aligned input rows: staged through the ring
+  if (aligned_to(in, 16) && in_pitch % 16 == 0 && k_bytes <= 8192 - 16)
     return launch_ring<T, MODE>(in, out, batch, D, kk, nullptr, nullptr, s);
   return launch_general<T, MODE>(in, out, batch, D, kk, nullptr, nullptr, s);
 }
@@ -277,8 +277,10 @@ template <typename T, int MODE>
 int launch_ring(const void* in, void* out, int64_t batch, int64_t D, int64_t k_dense, const int32_t* k_per_row,
                 const int64_t* out_offsets, cudaStream_t s) {
   const int64_t in_pitch = D * (int64_t)sizeof(T);
+  if (!(aligned_to(in, 16) && in_pitch % 16 == 0))
+    return launch_general<T, MODE>(in, out, batch, D, k_dense, k_per_row, out_offsets, s);
   constexpr int NCW = 4;
-  constexpr size_t smem = (size_t)NCW * 8192 + (size_t)NCW * 8 * 8 + (size_t)NCW * 8 * 4 * 4;
+  constexpr size_t smem = (size_t)NCW * 8192 + (size_t)NCW * 8 * 8 + (size_t)NCW * 8 * 3 * 4;
   auto kern = rows_ring_kernel<T, NCW, MODE>;
   {
     static std::atomic<uint64_t> done{0};

@@ -539,9 +539,8 @@ rows_bulk_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t ba
 // rolled passes, so the instruction count follows the row's real length and the kernel needs
 // few registers (a register-resident version sized for the longest row ran 777 instructions
 // per row at 12 warps per SM and was issue-bound at 3.1-3.7 TB/s).
-// Nothing but element alignment is required: a prefix that is not a multiple of 16 bytes, or
-// a row that starts off a 16-byte boundary (odd D), is staged as the aligned span around it
-// and processed element-wise.  Dense batches with such a k use
+// Only the input rows have to be 16-byte aligned: a prefix that is not a multiple of 16
+// bytes is staged rounded up and processed element-wise.  Dense batches with such a k use
 // this kernel too (k_per_row == out_offsets == nullptr).  A row longer than the ring takes
 // general_row.
 template <typename T, int NCW, int MODE>
@@ -553,12 +552,12 @@ rows_ring_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t ba
   constexpr int RING = PAGE * P;
   extern __shared__ __align__(128) unsigned char ring[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(ring + (size_t)NCW * RING);
-  int* meta = reinterpret_cast<int*>(bars + NCW * R);   // [NCW][R][4]: page, bytes staged, pages held, lead bytes
+  int* meta = reinterpret_cast<int*>(bars + NCW * R);   // [NCW][R][3]: page, bytes, pages held
   const int lane = threadIdx.x & 31;
   const int wib = threadIdx.x >> 5;
   unsigned char* my_ring = ring + (size_t)wib * RING;
   const uint32_t bar0 = smem_u32(&bars[wib * R]);
-  int* my_meta = meta + wib * R * 4;
+  int* my_meta = meta + wib * R * 3;
 
   if (lane == 0) {
 #pragma unroll
@@ -569,22 +568,16 @@ rows_ring_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t ba
   __syncthreads();
   pdl_prologue();
 
-  // Bytes of row `row` to stage: the 16-byte aligned span that covers its prefix (`lead`
-  // bytes of the previous row in front when the row itself starts off a 16-byte boundary, up
-  // to 15 bytes of the row's own tail or of the next row behind), or 0 when that span does not
-  // fit the ring or would reach outside the caller's matrix (first/last row of an unaligned
-  // one).  k_per_row == nullptr: every row keeps k_dense; out_offsets == nullptr: dense.
-  const char* const in_end = in + batch * in_pitch;
-  auto row_plan = [&](int64_t row, char*& dst, int64_t& kr, int& lead) -> uint32_t {
+  // Bytes of row `row` to stage: its prefix rounded up to 16 (the input rows are 16-byte
+  // aligned and pitched, so the round-up stays inside the row), or 0 when it does not fit
+  // the ring.  k_per_row == nullptr: every row keeps k_dense; out_offsets == nullptr: dense.
+  auto row_plan = [&](int64_t row, char*& dst, int64_t& kr) -> uint32_t {
     kr = k_per_row ? (int64_t)k_per_row[row] : k_dense;
     if (kr > D) kr = D;
     const int64_t kb = kr * (int64_t)sizeof(T);
     dst = out + (out_offsets ? out_offsets[row] : row * kr) * (int64_t)sizeof(T);
-    const char* src = in + row * in_pitch;
-    lead = (int)(reinterpret_cast<uintptr_t>(src) & 15);
-    const int64_t staged = (lead + kb + 15) & ~(int64_t)15;
-    const bool ok = kb > 0 && staged <= (int64_t)RING && src - lead >= in && src - lead + staged <= in_end;
-    return ok ? (uint32_t)staged : 0u;
+    const int64_t staged = (kb + 15) & ~(int64_t)15;
+    return (kb > 0 && staged <= (int64_t)RING) ? (uint32_t)staged : 0u;
   };
 
   uint64_t policy;
@@ -597,20 +590,19 @@ rows_ring_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t ba
   int head_page = 0, used = 0, inflight = 0;
   auto issue_more = [&]() {
     while (head_row < end && inflight < R) {
-      char* d; int64_t kr; int lead;
-      const uint32_t nb = row_plan(head_row, d, kr, lead);
+      char* d; int64_t kr;
+      const uint32_t nb = row_plan(head_row, d, kr);
       const int slot = (int)((head_row - first) % R);
       if (nb == 0) {
-        my_meta[slot * 4 + 1] = 0; my_meta[slot * 4 + 2] = 0;
+        my_meta[slot * 3 + 1] = 0; my_meta[slot * 3 + 2] = 0;
       } else {
         const int need = (int)((nb + PAGE - 1) / PAGE);
         if (used == 0) head_page = 0;                   // empty ring: any row that fits at all fits at 0
         int pos = head_page, waste = 0;
         if (pos + need > P) { waste = P - pos; pos = 0; }
         if (used + waste + need > P) break;
-        bulk_load_row(smem_u32(my_ring + pos * PAGE), in + head_row * in_pitch - lead, nb, bar0 + 8u * slot, policy);
-        my_meta[slot * 4] = pos; my_meta[slot * 4 + 1] = (int)nb; my_meta[slot * 4 + 2] = waste + need;
-        my_meta[slot * 4 + 3] = lead;
+        bulk_load_row(smem_u32(my_ring + pos * PAGE), in + head_row * in_pitch, nb, bar0 + 8u * slot, policy);
+        my_meta[slot * 3] = pos; my_meta[slot * 3 + 1] = (int)nb; my_meta[slot * 3 + 2] = waste + need;
         used += waste + need;
         head_page = pos + need == P ? 0 : pos + need;
       }
@@ -623,11 +615,11 @@ rows_ring_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t ba
   for (int64_t row = first; row < end; ++row) {
     __syncwarp();                                       // lane 0's bookkeeping is visible
     const int slot = (int)((row - first) % R);
-    const int pos = my_meta[slot * 4];
-    const uint32_t row_bytes = (uint32_t)my_meta[slot * 4 + 1];
-    const int held = my_meta[slot * 4 + 2];
-    char* dst; int64_t kr; int lead;
-    row_plan(row, dst, kr, lead);
+    const int pos = my_meta[slot * 3];
+    const uint32_t row_bytes = (uint32_t)my_meta[slot * 3 + 1];
+    const int held = my_meta[slot * 3 + 2];
+    char* dst; int64_t kr;
+    row_plan(row, dst, kr);
     if (row_bytes == 0) {                               // warp-uniform: odd row, nothing staged
       __syncwarp();
       if (lane == 0) { --inflight; issue_more(); }
@@ -639,12 +631,12 @@ rows_ring_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t ba
     const int nvec16 = (int)(row_bytes >> 4);
     const uint4* src = reinterpret_cast<const uint4*>(my_ring + pos * PAGE);
     uint4* dst4 = reinterpret_cast<uint4*>(dst);
-    const bool vec_ok = lead == 0 && ((kr * (int64_t)sizeof(T)) % 16 == 0) && (reinterpret_cast<uintptr_t>(dst) % 16) == 0;
+    const bool vec_ok = ((kr * (int64_t)sizeof(T)) % 16 == 0) && (reinterpret_cast<uintptr_t>(dst) % 16) == 0;
 
     if (!vec_ok) {
       // odd k, or an output row that is not 16-byte aligned: same two passes over the staged
       // row, element by element (coalesced 4/8-byte accesses)
-      const T* xs = reinterpret_cast<const T*>(reinterpret_cast<const unsigned char*>(src) + lead);
+      const T* xs = reinterpret_cast<const T*>(src);
       T* y = reinterpret_cast<T*>(dst);
       const int n = (int)kr;
       if constexpr (MODE == kModeTruncate) {
