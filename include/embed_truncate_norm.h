@@ -191,6 +191,11 @@ ETN_API int64_t etn_json_truncate_response(const char *json, size_t len, int64_t
                                            char *out, size_t out_cap, int n_devices,
                                            int64_t *stats);
 
+/* result["usage"]["prompt_tokens"] as proxyOpenAIEmbed extracts it for the token metric
+ * (handlers.go:2052-2057: a float64 converted with int()); 0 when absent or not a number,
+ * ETN_ERR_JSON for malformed text.  Lets the handler skip the map decode altogether. */
+ETN_API int64_t etn_json_prompt_tokens(const char *json, size_t len);
+
 /* "[a,b,c]" -> up to max_n float64 values, correctly rounded like strconv.ParseFloat (the
  * decoder's number path at handlers.go:2048); numbers past max_n are validated and skipped.
  * Returns the element count of the array or a negative code. */

@@ -452,6 +452,57 @@ int64_t etn_json_parse_array(const char* text, size_t len, double* dst, int64_t 
   }
 }
 
+int64_t etn_json_prompt_tokens(const char* json, size_t len) {
+  if (!json) return ETN_ERR_NULL;
+  Scanner sc{json, json + len, json};
+  sc.ws();
+  if (sc.p >= sc.e || *sc.p != '{') return 0;
+  ++sc.p; sc.ws();
+  if (sc.p < sc.e && *sc.p == '}') return 0;
+  int64_t tokens = 0;                              // Go keeps the last duplicate; so does this loop
+  for (;;) {
+    sc.ws();
+    bool is_usage = false;
+    if (!sc.string_is("usage", &is_usage)) return ETN_ERR_JSON;
+    sc.ws();
+    if (sc.p >= sc.e || *sc.p != ':') return ETN_ERR_JSON;
+    ++sc.p; sc.ws();
+    if (is_usage) tokens = 0;
+    if (is_usage && sc.p < sc.e && *sc.p == '{') {
+      ++sc.p; sc.ws();
+      if (sc.p < sc.e && *sc.p == '}') { ++sc.p; }
+      else for (;;) {
+        sc.ws();
+        bool is_pt = false;
+        if (!sc.string_is("prompt_tokens", &is_pt)) return ETN_ERR_JSON;
+        sc.ws();
+        if (sc.p >= sc.e || *sc.p != ':') return ETN_ERR_JSON;
+        ++sc.p; sc.ws();
+        const char* v0 = sc.p;
+        const bool num = sc.p < sc.e && (*sc.p == '-' || (*sc.p >= '0' && *sc.p <= '9'));
+        if (!sc.skip_value(2)) return ETN_ERR_JSON;
+        if (is_pt) {
+          tokens = 0;
+          if (num) {
+            double d = 0;
+            auto r = std::from_chars(v0, sc.p, d);
+            if (r.ec == std::errc() && std::fabs(d) < 9.2e18) tokens = (int64_t)d;   // int(pt): truncation toward zero
+          }
+        }
+        sc.ws();
+        if (sc.p < sc.e && *sc.p == ',') { ++sc.p; continue; }
+        if (sc.p < sc.e && *sc.p == '}') { ++sc.p; break; }
+        return ETN_ERR_JSON;
+      }
+    } else if (!sc.skip_value(1)) return ETN_ERR_JSON;
+    sc.ws();
+    if (sc.p < sc.e && *sc.p == ',') { ++sc.p; continue; }
+    if (sc.p < sc.e && *sc.p == '}') break;
+    return ETN_ERR_JSON;
+  }
+  return tokens;
+}
+
 int64_t etn_json_truncate_response(const char* json, size_t len, int64_t dims, int mode, char* out,
                                    size_t out_cap, int n_devices, int64_t* stats) {
   const bool b64 = (mode & ETN_JSON_BASE64) != 0;

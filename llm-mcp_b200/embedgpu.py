@@ -36,7 +36,7 @@ EXPORTS = (
     "embed_truncate_norm_ragged", "etn_init", "etn_shutdown", "etn_device_count",
     "etn_alloc_pinned", "etn_free_pinned", "embed_truncate_norm_host", "etn_fill_synthetic",
     "embed_truncate_norm_host_static",
-    "etn_json_truncate_response", "etn_json_parse_array", "etn_json_format_array",
+    "etn_json_truncate_response", "etn_json_parse_array", "etn_json_format_array", "etn_json_prompt_tokens",
     "etn_get_counters", "etn_counter_name",
 )
 
@@ -82,6 +82,8 @@ def lib() -> ctypes.CDLL:
         L.etn_json_parse_array.restype = i64
         L.etn_json_format_array.argtypes = [vp, i64, vp, ctypes.c_size_t]
         L.etn_json_format_array.restype = i64
+        L.etn_json_prompt_tokens.argtypes = [ctypes.c_char_p, ctypes.c_size_t]
+        L.etn_json_prompt_tokens.restype = i64
         L.etn_get_counters.argtypes = [vp, ci]
         L.etn_counter_name.argtypes = [ci]
         L.etn_counter_name.restype = ctypes.c_char_p
@@ -303,6 +305,14 @@ def truncate_response_json(body: bytes, dims: int, renorm: bool | None = None, n
         code = int(n) if n > -1000 else int(-1000 - n)
         raise EtnError(code, strerror(code), "etn_json_truncate_response")
     return out.raw[:n], {"gpu_vectors": stats[0], "resliced_vectors": stats[1], "arrays": stats[2]}
+
+
+def prompt_tokens(body: bytes) -> int:
+    """usage.prompt_tokens the way proxyOpenAIEmbed reads it (handlers.go:2052-2057)."""
+    n = lib().etn_json_prompt_tokens(body, len(body))
+    if n < 0 and n in (ERR_JSON, ERR_NULL):
+        raise EtnError(int(n), strerror(int(n)), "etn_json_prompt_tokens")
+    return int(n)
 
 
 # ------------------------------------------------------------------- counters (N3) ----

@@ -40,6 +40,7 @@ int main() {
         default: s.resize(pos); break;
       }
     }
+    { char* in = (char*)malloc(s.size() ? s.size() : 1); memcpy(in, s.data(), s.size()); (void)etn_json_prompt_tokens(in, s.size()); free(in); }
     for (int mode : {ETN_TRUNCATE, ETN_TRUNCATE_RENORM, ETN_TRUNCATE | ETN_JSON_BASE64, ETN_TRUNCATE_RENORM | ETN_JSON_BASE64}) {
       for (int64_t dims : {1, 2, 4}) {
         // exact-size heap copies so that ASan sees any read past the end of the input

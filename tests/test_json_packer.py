@@ -202,3 +202,16 @@ def test_fuzz_random_json_matches_reference(oracle):
         for dims in (1, 3, 8):
             out, _ = eg.truncate_response_json(body, dims, renorm=False)
             assert json.loads(out) == oracle.response_ref(body, dims, renorm=False), (trial, dims, body)
+
+
+def test_prompt_tokens_like_the_handler():
+    """handlers.go:2052-2057: usage.prompt_tokens is read as float64 and converted with int()."""
+    f = eg.prompt_tokens
+    assert f(b'{"data":[],"usage":{"prompt_tokens":17,"total_tokens":17}}') == 17
+    assert f(b'{"usage":{"total_tokens":3, "prompt_tokens" : 12.9 }, "data":[{"embedding":[1,2]}]}') == 12
+    assert f(b'{"usage":{"prompt_tokens":"17"}}') == 0 and f(b'{"usage":17}') == 0 and f(b'{"data":[]}') == 0 and f(b'[1]') == 0
+    assert f(b'{"x":{"usage":{"prompt_tokens":5}}}') == 0                       # only the top-level usage counts
+    assert f(b'{"usage":{"prompt_tokens":1},"usage":{"prompt_tokens":2}}') == 2   # last duplicate wins, as in Go
+    assert f(b'{"usage":{"prompt_tokens":-3.5}}') == -3
+    with pytest.raises(eg.EtnError):
+        f(b'{"usage":{"prompt_tokens":1}')
