@@ -202,6 +202,30 @@ static void pcie_study(Timer& tm) {
     ms = tm.ms([&](int) { kern<<<g, kThreads>>>(hin, hout, rows, D * es, nvec); }, 1, 5);
     rep(nm, ms, pre_bytes);
   }
+  // hybrid: the kernel reads the host input itself (no H2D DMA) while the copy engine drains
+  // the previous chunk's output D2H
+  {
+    cudaEvent_t a, b, c; CK(cudaEventCreate(&a)); CK(cudaEventCreate(&b)); CK(cudaEventCreate(&c));
+    CK(cudaDeviceSynchronize());
+    CK(cudaEventRecord(a, s1)); CK(cudaStreamWaitEvent(s2, a));
+    for (int i = 0; i < 5; ++i) {
+      kern<<<grid, kThreads, 0, s1>>>(hin, dout, rows, D * es, nvec);
+      CK(cudaMemcpyAsync(hout, din, pre_bytes, cudaMemcpyDeviceToHost, s2));
+    }
+    CK(cudaEventRecord(c, s2)); CK(cudaStreamWaitEvent(s1, c)); CK(cudaEventRecord(b, s1));
+    CK(cudaEventSynchronize(b));
+    float t; CK(cudaEventElapsedTime(&t, a, b));
+    rep("hybrid: zero-copy read kernel || D2H DMA (each direction)", t / 5, pre_bytes);
+    CK(cudaEventRecord(a, s1)); CK(cudaStreamWaitEvent(s2, a));
+    for (int i = 0; i < 5; ++i) {
+      CK(cudaMemcpy2DAsync(din, k * es, hin, D * es, k * es, rows, cudaMemcpyHostToDevice, s1));
+      kern<<<grid, kThreads, 0, s2>>>(dout, hout, rows, k * es, nvec);
+    }
+    CK(cudaEventRecord(c, s2)); CK(cudaStreamWaitEvent(s1, c)); CK(cudaEventRecord(b, s1));
+    CK(cudaEventSynchronize(b));
+    CK(cudaEventElapsedTime(&t, a, b));
+    rep("hybrid: H2D DMA || zero-copy write kernel (each direction)", t / 5, pre_bytes);
+  }
   // small request latency: C1 1024 x 4096 f64 -> 1024 (8 MiB each way)
   {
     auto k64 = rows_reg_kernel<double, 32, 8, 1, 32, 1, 2, 1>;
