@@ -114,6 +114,28 @@ def test_dense_against_oracle(oracle, rows, D, k, dt, seed):
 
 
 @pytest.mark.parametrize("dt", [np.float32, np.float64])
+def test_dispatch_boundaries(oracle, dt):
+    """Every size at which the dispatcher changes kernel or tiling (lanes per row, vectors per
+    lane, bulk ring, wide rows, the 112 KiB limit), one step below, at, and one step above,
+    with k < D and k == D, 16- and 32-byte aligned pitches."""
+    es = np.dtype(dt).itemsize
+    edges = [16, 32, 256, 512, 1024, 2048, 4096, 6144, 8192, 16384, 57344, 114688]
+    rows = 37
+    for kb in edges:
+        for delta in (-16, 0, 16, es):
+            k = (kb + delta) // es
+            if k <= 0:
+                continue
+            for D in (k, k + 16 // es, k + 32 // es + (32 // es) * 3):
+                xh = oracle.fill(kb % 97 + 1, rows, D, dt)
+                x = gu.to_dev(xh)
+                tr = gu.run_dense(x, k, eg.TRUNCATE).cpu().numpy()
+                assert np.array_equal(gu.bits(tr), gu.bits(xh[:, :k])), (kb, delta, D)
+                rn = gu.run_dense(x, k, eg.TRUNCATE_RENORM).cpu().numpy()
+                assert_ulp(oracle, rn, oracle.renorm_exact(xh, k), what=f"k_bytes={kb}{delta:+d} D={D}")
+
+
+@pytest.mark.parametrize("dt", [np.float32, np.float64])
 def test_random_mantissas_and_scales(oracle, dt):
     """Full-mantissa values over a wide range of row magnitudes, including rows whose squares
     overflow or underflow the element type."""

@@ -304,11 +304,8 @@ int main(int argc, char** argv) {
   }
 
   std::vector<Shape> shapes = {
-      {"MIDf64 256Kx3072->1536", 262144, 3072, 1536, 8},
-      {"BIGf64 128Kx4096->4096", 131072, 4096, 4096, 8},
-      {"BIGf32 256Kx4096->4096", 262144, 4096, 4096, 4},
-      {"HUGEf32 64Kx16384->16384", 65536, 16384, 16384, 4},
-      {"WIDEf64 32Kx16384->12288", 32768, 16384, 12288, 8},
+      {"C3f32 1Mx4096->1024", 1048576, 4096, 1024, 4},
+      {"C4f32 2Mx3072->256", 2097152, 3072, 256, 4},
   };
   for (const Shape& s : shapes) {
     void *in, *out;
@@ -319,20 +316,24 @@ int main(int argc, char** argv) {
     CK(cudaDeviceSynchronize());
     const int64_t kb = s.k * s.es;
     void* out2; CK(cudaMalloc(&out2, (size_t)s.rows * s.k * s.es));
-    // cooperative register kernel vs wide-row shared-memory kernel
-    const size_t nel = (size_t)s.rows * s.k;
-    if (s.es == 8 && kb == 12288) {
-      for (int rpb : {2, 4, 8}) run_wide<double, 1>(s, in, out2, tm, rpb);
-      run_wide<double, 0>(s, in, out2, tm, 4);
-    } else if (s.es == 8 && kb == 32768) {
-      for (int rpb : {2, 4, 8}) run_wide<double, 1>(s, in, out2, tm, rpb);
-    } else if (s.es == 4 && kb == 16384) {
-      for (int rpb : {2, 4, 8}) run_wide<float, 1>(s, in, out2, tm, rpb);
-    } else if (s.es == 4 && kb == 65536) {
-      for (int rpb : {2, 4}) run_wide<float, 1>(s, in, out2, tm, rpb);
-    } else if (s.es == 8 && kb == 98304) {
-      for (int rpb : {2, 4}) run_wide<double, 1>(s, in, out2, tm, rpb);
-      run_wide<double, 0>(s, in, out2, tm, 4);
+    if (s.es == 4 && kb == 4096) {
+      run_reg<float, 32, 4, 1, 1, 4, 1>(s, in, out, tm, 0);
+      run_reg<float, 32, 4, 2, 1, 2, 1>(s, in, out, tm, 0);
+      run_bulk<float, 8, 2, 8, 1>(s, in, out2, tm, out, 8);
+      run_bulk<float, 8, 2, 8, 1>(s, in, out2, tm, out, 4);
+      run_bulk<float, 8, 3, 8, 1>(s, in, out2, tm, out, 8);
+      run_bulk<float, 8, 2, 4, 1>(s, in, out2, tm, out, 8);
+      run_bulk<float, 8, 2, 4, 1>(s, in, out2, tm, out, 4);
+      run_bulk<float, 8, 4, 4, 1>(s, in, out2, tm, out, 8);
+      run_bulk<float, 8, 2, 8, 0>(s, in, out2, tm, nullptr, 8);
+      run_reg<float, 32, 4, 1, 0, 4, 1>(s, in, out, tm, 0);
+    } else if (s.es == 4 && kb == 1024) {
+      run_reg<float, 32, 1, 4, 1, 4, 1>(s, in, out, tm, 0);
+      run_reg<float, 32, 1, 8, 1, 2, 1>(s, in, out, tm, 0);
+      run_bulk<float, 2, 4, 4, 1>(s, in, out2, tm, out, 16);
+      run_bulk<float, 2, 4, 8, 1>(s, in, out2, tm, out, 8);
+      run_bulk<float, 2, 8, 4, 1>(s, in, out2, tm, out, 16);
+      run_bulk<float, 2, 4, 4, 1>(s, in, out2, tm, out, 8);
     }
     CK(cudaFree(out2));
     CK(cudaFree(in)); CK(cudaFree(out));
