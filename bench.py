@@ -346,21 +346,33 @@ def run_ours(args, wl, rank, local_rank, world):
 
     for i in range(args.warmup):
         step(i)
-    sampler = ClockSampler(physical_gpu_index(local_rank))
-    barrier()
-    launches0 = eg.counters()["llmcore_embed_gpu_kernel_launches_total"]
-    sampler.start()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record()
-    for i in range(args.steps):
-        step(i)
-    ev1.record()
-    barrier()
-    clocks = sampler.stop()
-    gpu_launches = eg.counters()["llmcore_embed_gpu_kernel_launches_total"] - launches0   # counted by the library
-    ms = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    # Timed region.  A run that saw a hardware or thermal slowdown is thrown away and measured
+    # once more (all ranks decide together); sw_power_cap is normal on a 1 kW part and is kept.
+    BAD = {"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"}
+    remeasured = False
+    for attempt in range(2):
+        sampler = ClockSampler(physical_gpu_index(local_rank))
+        barrier()
+        launches0 = eg.counters()["llmcore_embed_gpu_kernel_launches_total"]
+        sampler.start()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        for i in range(args.steps):
+            step(i)
+        ev1.record()
+        barrier()
+        clocks = sampler.stop()
+        gpu_launches = eg.counters()["llmcore_embed_gpu_kernel_launches_total"] - launches0   # counted by the library
+        ms = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device="cuda")
+        bad = torch.tensor([1.0 if BAD & set(clocks["reasons"]) else 0.0], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+            dist.all_reduce(bad, op=dist.ReduceOp.MAX)
+        if float(bad.item()) == 0.0 or attempt == 1:
+            break
+        remeasured = True
+        time.sleep(2.0)
+    clocks["remeasured"] = remeasured
     ms_total = float(ms.item())
     value = world * rows * args.steps / (ms_total * 1e-3)
 
