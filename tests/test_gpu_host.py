@@ -182,7 +182,8 @@ def test_typed_vectors_ollama_branch(oracle):
     d = {k: after[k] - before[k] for k in after}
     assert d["llmcore_embed_gpu_host_calls_total"] == 4 and d["llmcore_embed_gpu_host_rows_total"] == 16
     assert d["llmcore_embed_gpu_h2d_bytes_total"] == 16 * 256 * 8 == d["llmcore_embed_gpu_d2h_bytes_total"]
-    assert d["llmcore_embed_gpu_kernel_launches_total"] == 2 and d["llmcore_embed_gpu_errors_total"] == 0
+    nd = eg.lib().etn_device_count()                 # the 7-row group is sharded over every bound device
+    assert d["llmcore_embed_gpu_kernel_launches_total"] == min(nd, 7) + 1 and d["llmcore_embed_gpu_errors_total"] == 0
 
 
 def test_json_packer_base64_renorm(oracle):
