@@ -374,8 +374,8 @@ void destroy_ctx(DevCtx* c) {
 // Processes rows [0, rows) of one device's block.  host_in/host_out already point at the
 // block.  Every chunk runs H2D -> kernel (in place on the dense staging tile) -> D2H on its
 // slot's stream; the slots keep both copy engines and the SMs busy at once.
-int run_block(DevCtx* c, int64_t rows, int64_t D, int64_t kk, int dtype, int mode,
-              const char* host_in, int64_t in_pitch, char* host_out) {
+int run_block(DevCtx* c, int64_t rows, int64_t kk, int dtype, int mode, const char* host_in,
+              int64_t in_pitch, char* host_out) {
   std::lock_guard<std::mutex> lock(c->mu);
   cudaError_t e = cudaSetDevice(c->dev);
   if (e != cudaSuccess) return (int)e;
@@ -592,7 +592,7 @@ int embed_truncate_norm_host(int64_t batch, int64_t D, int64_t k, int dtype, int
   auto work = [&](int g) {
     const int64_t r0 = (int64_t)g * per, r1 = std::min(batch, r0 + per);
     if (r1 <= r0) return;
-    rcs[g] = run_block(ctx[g], r1 - r0, D, kk, dtype, mode, hin + r0 * in_pitch_bytes,
+    rcs[g] = run_block(ctx[g], r1 - r0, kk, dtype, mode, hin + r0 * in_pitch_bytes,
                        in_pitch_bytes, hout + r0 * kk * es);
   };
   if (n_devices == 1) {
