@@ -152,6 +152,50 @@ template <typename T> double max_rel_diff(const void* a, const void* b, size_t n
   return m;
 }
 
+// C1-sized launches (1,024 x 4096 f64 -> 1024, 16 MiB per launch): bulk ring (one row per warp)
+// against the wide-row kernel (a block per row), rotating buffers, programmatic dependent launch.
+static void c1_study(Timer& tm) {
+  const int64_t rows = 1024, D = 4096, k = 1024; const int es = 8, NSET = 8;
+  void* in[NSET]; void* out[NSET];
+  for (int i = 0; i < NSET; ++i) {
+    CK(cudaMalloc(&in[i], (size_t)rows * D * es)); CK(cudaMalloc(&out[i], (size_t)rows * k * es));
+    fill_kernel<double><<<g_sms * 16, 256>>>((double*)in[i], 3 + i, 0, rows, D, D, D);
+  }
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  const int nvec16 = (int)(k * es / 16);
+  auto report = [&](const char* nm, double ms) { printf("%-60s %7.2f us  %7.1f GB/s\n", nm, ms * 1e3, (double)rows * 2 * k * es / ms / 1e6); };
+  {
+    auto kern = rows_bulk_kernel<double, 16, 2, 4, 1>;
+    const size_t smem = (size_t)4 * 2 * 16 * 512 + 4 * 2 * 8;
+    CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    for (int rpw : {1, 2}) {
+      cudaLaunchConfig_t cfg = {}; cfg.gridDim = dim3((unsigned)((rows + 4 * rpw - 1) / (4 * rpw))); cfg.blockDim = dim3(128);
+      cfg.dynamicSmemBytes = smem; cfg.attrs = attr; cfg.numAttrs = 1;
+      double ms = tm.ms([&](int i) { CK(cudaLaunchKernelEx(&cfg, kern, (const char*)in[i % NSET], (char*)out[i % NSET], rows, D * es, nvec16, rpw)); }, 10, 400);
+      char nm[96]; snprintf(nm, sizeof nm, "C1 bulk<double,16,2,4> rpw=%d grid=%u", rpw, cfg.gridDim.x); report(nm, ms);
+    }
+  }
+  {
+    auto kern = rows_wide_kernel<double, 1>;
+    const size_t smem = 2 * (size_t)8192;
+    for (int rpb : {1, 2}) {
+      cudaLaunchConfig_t cfg = {}; cfg.gridDim = dim3((unsigned)((rows + rpb - 1) / rpb)); cfg.blockDim = dim3(kThreads);
+      cfg.dynamicSmemBytes = smem; cfg.attrs = attr; cfg.numAttrs = 1;
+      double ms = tm.ms([&](int i) { CK(cudaLaunchKernelEx(&cfg, kern, (const char*)in[i % NSET], (char*)out[i % NSET], rows, D * es, nvec16, rpb)); }, 10, 400);
+      char nm[96]; snprintf(nm, sizeof nm, "C1 wide<double> rpb=%d grid=%u", rpb, cfg.gridDim.x); report(nm, ms);
+    }
+  }
+  {
+    auto kern = rows_reg_kernel<double, 32, 8, 1, 32, 1, 2, 1>;
+    cudaLaunchConfig_t cfg = {}; cfg.gridDim = dim3((unsigned)(rows / 8)); cfg.blockDim = dim3(kThreads); cfg.attrs = attr; cfg.numAttrs = 1;
+    double ms = tm.ms([&](int i) { CK(cudaLaunchKernelEx(&cfg, kern, (const char*)in[i % NSET], (char*)out[i % NSET], rows, D * es, (int)(k * es / 32))); }, 10, 400);
+    report("C1 reg<double,32,8,1> grid=128", ms);
+  }
+  for (int i = 0; i < NSET; ++i) { cudaFree(in[i]); cudaFree(out[i]); }
+}
+
 // PCIe study for the host path: DMA ceilings, prefix-only 2-D DMA, and the kernels reading and
 // writing pinned host memory directly (zero copy).  C3 slice: rows x 4096 f32 -> 1024.
 static void pcie_study(Timer& tm) {
@@ -275,6 +319,7 @@ int main(int argc, char** argv) {
   printf("device %s, %d SMs, L2 %d MiB\n", p.name, g_sms, p.l2CacheSize >> 20);
   Timer tm;
   if (g_filter && !strcmp(g_filter, "pcie")) { pcie_study(tm); return 0; }
+  if (g_filter && !strcmp(g_filter, "c1")) { c1_study(tm); return 0; }
   if (g_filter && !strcmp(g_filter, "small")) {
     for (bool pdl : {false, true}) {
       run_reg_small<float, 32, 1, 4, 1, 4, 32>("C2 64Kx768->256", 65536, 768, 256, 4, tm, pdl);
