@@ -30,7 +30,8 @@
  *   - Device entry points work on the calling thread's current CUDA device and enqueue
  *     on `stream` (a cudaStream_t; NULL = the legacy default stream) without
  *     synchronising.  They allocate nothing and keep no pointer.
- *   - `in` and `out` must not overlap, except out == in with k >= D (normalise in place).
+ *   - `in` and `out` must not overlap, except out == in with k >= D (normalise in place;
+ *     out == in with k < D is refused with ETN_ERR_SHAPE).
  *   - Every entry point is re-entrant and may be called from any OS thread (Go handlers
  *     run on arbitrary threads).
  */
@@ -50,7 +51,7 @@ extern "C" {
 #define ETN_API
 #endif
 
-#define ETN_VERSION 100 /* 0.1.0 */
+#define ETN_VERSION 200 /* 0.2.0 */
 
 #define ETN_F32 0
 #define ETN_F64 1
@@ -69,6 +70,7 @@ extern "C" {
 #define ETN_ERR_JSON (-8)      /* malformed JSON, a non-finite value, or a number outside float64 */
 #define ETN_ERR_JSON_DUP (-9)  /* "data" or an item's "embedding" occurs twice: take the reference path */
 #define ETN_ERR_TOO_LARGE (-7) /* more than ETN_STATIC_STAGE_BYTES asked of the _static entry point */
+#define ETN_ERR_TICKET (-10)   /* etn_wait: unknown ticket, or one that was already waited for */
 
 /* Library version (ETN_VERSION of the build).  No reference counterpart. */
 ETN_API int etn_version(void);
@@ -98,12 +100,31 @@ ETN_API int embed_truncate_norm_ragged(int64_t batch, int64_t D, const int32_t *
                                const int64_t *out_offsets, int dtype, int mode, const void *in,
                                void *out, void *stream);
 
+/* Many requests, one launch, device-resident: row r is the k_per_row[r] elements that start at
+ * element in_offsets[r] of in_base and is written at element out_offsets[r] of out_base (all
+ * three arrays in device memory, `batch` entries; k_per_row already holds min(dims, len) —
+ * handlers.go:2074 — because rows of different requests have different lengths).  This is the
+ * launch the host runtime issues when it coalesces concurrent handlers (north_star item 2,
+ * "one launch per batch"; handlers run one goroutine per connection, server.go:54), exposed
+ * for callers whose vectors already live on the GPU.  Row starts must be 16-byte aligned. */
+ETN_API int embed_truncate_norm_gather(int64_t batch, const int64_t *in_offsets,
+                                       const int32_t *k_per_row, const int64_t *out_offsets,
+                                       int dtype, int mode, const void *in_base, void *out_base,
+                                       void *stream);
+
 /* ---- host path: what the handler calls between proxyOpenAIEmbed (handlers.go:1879) and
  * WriteJSON (handlers.go:1894) once the response vectors are packed in host memory. ---- */
 
-/* Creates per-device streams, events and staging buffers.  device_ids == NULL or
- * n_devices == 0 selects every visible device.  Call once from main (the reference wires
- * its components at core/cmd/core/main.go:49-51).  Calling it again is a no-op. */
+/* Creates, per device, a worker thread, four streams with their events and four staging slots
+ * (64 MiB in + 64 MiB out each).  device_ids == NULL or n_devices == 0 selects every visible
+ * device.  Call once from main (the reference wires its components at
+ * core/cmd/core/main.go:49-51).  Calling it again is a no-op.  Environment, read here the way
+ * config.Getenv reads its knobs (config.go:9-24):
+ *   EMBED_GPU_MAX_WAIT_US        how long a worker that holds one small request waits for
+ *                                others to share its launch (default 0: only requests that
+ *                                are already queued are merged)
+ *   EMBED_GPU_MIN_DEVICE_BYTES   kept-prefix bytes a device must get before a call is split
+ *                                over one more device (default 4 MiB) */
 ETN_API int etn_init(const int *device_ids, int n_devices);
 
 /* Releases what etn_init created (main.go:118-122, graceful shutdown). */
@@ -120,16 +141,54 @@ ETN_API void *etn_alloc_pinned(size_t bytes);
 ETN_API void etn_free_pinned(void *p);
 
 /* End to end on host buffers, synchronous — the call that replaces
- * truncateEmbeddings(result, dims) at handlers.go:1891-1893: rows are split into contiguous blocks over the
- * first n_devices devices of etn_init (0 = all of them), each block is copied prefix-only
- * (kk of D columns) to its device in chunks, processed and copied back, with the copies
- * of one chunk overlapping the kernel of another.  host_in is [batch x D] with a row
- * pitch of in_pitch_bytes (>= D * elem size, or 0 for dense); host_out is dense
- * [batch x kk].  Pinned buffers (etn_alloc_pinned) give full PCIe speed; pageable memory
- * works but is slower.  No collective is involved: rows are independent. */
+ * truncateEmbeddings(result, dims) at handlers.go:1891-1893.  The rows are split into
+ * contiguous blocks over at most n_devices of the devices etn_init bound (0 = all of them;
+ * the least loaded ones are taken, and a call brings in one more device only for every
+ * EMBED_GPU_MIN_DEVICE_BYTES of kept prefixes, so a request-sized batch stays on one GPU and
+ * concurrent requests spread over the box).  Each block is queued to its device's worker, which
+ * copies it prefix-only (kk of D columns) in chunks, processes it and copies it back, the
+ * copies of one chunk overlapping the kernel of another; small requests of several callers
+ * that are queued together share one chunk and one launch.  host_in is [batch x D] with a row
+ * pitch of in_pitch_bytes (>= D * elem size, or 0 for dense); host_out is dense [batch x kk]
+ * and may be host_in itself when in_pitch_bytes == kk * elem size.  Pinned buffers
+ * (etn_alloc_pinned) give full PCIe speed; pageable memory works but is slower.  No
+ * collective is involved: rows are independent. */
 ETN_API int embed_truncate_norm_host(int64_t batch, int64_t D, int64_t k, int dtype, int mode,
                              const void *host_in, int64_t in_pitch_bytes, void *host_out,
                              int n_devices);
+
+/* Ragged batch end to end on host buffers, synchronous: row r keeps kr = min(k_per_row[r], D)
+ * components and the results are packed back to back in row order (row r at element
+ * sum_{i<r} k_i of host_out_packed).  This is what a handler-side batcher hands over when it
+ * has merged responses of requests that resolved different `dimensions`
+ * (handlers.go:1874-1877 resolves dims per request; handlers.go:2068-2076 treats every vector
+ * on its own).  The rows are cut into contiguous ranges balanced by kept bytes, not by row
+ * count (the cost of a row is its k), over at most n_devices devices; runs of rows with one k
+ * travel as one prefix-only 2-D copy each.  k_per_row is host memory; every k must be
+ * positive (ETN_ERR_SHAPE otherwise, like k <= 0 in the dense calls: the handler only calls
+ * with dims > 0, handlers.go:1891). */
+ETN_API int embed_truncate_norm_ragged_host(int64_t batch, int64_t D, const int32_t *k_per_row,
+                                            int dtype, int mode, const void *host_in,
+                                            int64_t in_pitch_bytes, void *host_out_packed,
+                                            int n_devices);
+
+/* The cut points embed_truncate_norm_ragged_host uses: cuts[0..n_shards] with shard g =
+ * rows [cuts[g], cuts[g+1]), balanced by sum of min(k, D).  For callers that shard a
+ * ragged batch themselves (one process per GPU).  No reference counterpart. */
+ETN_API int etn_shard_ragged(int64_t batch, int64_t D, const int32_t *k_per_row, int n_shards,
+                             int64_t *cuts);
+
+/* The two host calls above without the wait: *ticket receives a handle, the buffers must stay
+ * untouched until etn_wait(ticket) returns the call's result (each ticket is waited for
+ * exactly once).  k_per_row == NULL selects the dense form with `k`, otherwise `k` is
+ * ignored.  A handler that has several responses in hand — or a batcher goroutine serving
+ * many connections — submits them all and then waits, so the device workers see the whole
+ * queue and merge it into few launches (north_star item 2).  No reference counterpart: the
+ * reference handles one response per goroutine (handlers.go:1891-1893). */
+ETN_API int etn_submit_host(int64_t batch, int64_t D, int64_t k, const int32_t *k_per_row, int dtype,
+                            int mode, const void *host_in, int64_t in_pitch_bytes, void *host_out,
+                            int n_devices, int64_t *ticket);
+ETN_API int etn_wait(int64_t ticket);
 
 /* Size of the staging array built into the library image: 16 MiB of device memory on every
  * GPU that loads the library, held until the process exits. */
@@ -159,7 +218,8 @@ ETN_API int embed_truncate_norm_host(int64_t batch, int64_t D, int64_t k, int dt
  * All calls on a device share the one array, which keeps whatever the previous call left
  * in it; nothing in it has to be zero, since each call first overwrites the region it then
  * uses.  Two calls overlapping on the GPU would race on it, so the library holds a per-device
- * lock for the length of a call and concurrent callers queue. */
+ * lock for the length of a call and concurrent callers queue.  Calls and rows are counted
+ * with the host path's counters (ETN_CTR_HOST_*), a refused size with ETN_CTR_FALLBACKS. */
 ETN_API int embed_truncate_norm_host_static(int64_t batch, int64_t D, int64_t k, int dtype, int mode,
                                             const void *host_in, int64_t in_pitch_bytes,
                                             void *host_out, void *stream);
@@ -219,10 +279,38 @@ ETN_API int64_t etn_json_format_array(const double *v, int64_t n, char *buf, siz
 #define ETN_CTR_HOST_ROWS 4
 #define ETN_CTR_H2D_BYTES 5       /* bytes copied host -> device by the host path */
 #define ETN_CTR_D2H_BYTES 6
-#define ETN_CTR_ERRORS 7          /* non-zero returns (the handler then serves the reslice) */
-#define ETN_CTR_COUNT 8
+#define ETN_CTR_ERRORS 7          /* failed calls: CUDA errors and bad arguments */
+#define ETN_CTR_FALLBACKS 8       /* times the GPU path stepped aside and the reference path is to be
+                                     taken instead: ETN_ERR_JSON / _JSON_DUP / _TOO_LARGE / _NOT_INIT returns, and
+                                     vectors reported through etn_note_fallback */
+#define ETN_CTR_COALESCED 9       /* host-path requests that shared their launch with another request */
+#define ETN_CTR_COUNT 10
 ETN_API int etn_get_counters(int64_t *out, int capacity);
 ETN_API const char *etn_counter_name(int index);
+
+/* The wrapper's side of ETN_CTR_FALLBACKS: vectors it served with the reference reslice
+ * (handlers.go:2075) because they could not be packed (non-numeric elements) or because a
+ * call failed.  No reference counterpart. */
+ETN_API void etn_note_fallback(int64_t vectors);
+
+/* Fixed-bucket histograms, to be registered beside llmcore_embedding_duration_seconds
+ * (metrics.go:18-26; its buckets are at :23).  etn_get_histogram fills upper_bounds[i]
+ * (the last one is +Inf) and counts[i] = samples in bucket i (NOT cumulative; Prometheus'
+ * `le` series is the running sum) and returns the number of buckets; *sum receives the sum of
+ * all samples.  With both arrays NULL it only returns the number of buckets.  Kernel and
+ * copy times come from CUDA events the host path records around every staged chunk and reads
+ * when the chunk retires, so nothing synchronises for the sake of a metric. */
+#define ETN_HIST_BATCH_ROWS 0      /* rows per host-path call */
+#define ETN_HIST_KERNEL_SECONDS 1  /* kernel time per staged chunk */
+#define ETN_HIST_H2D_SECONDS 2     /* host-to-device copy time per staged chunk */
+#define ETN_HIST_D2H_SECONDS 3     /* device-to-host copy time per staged chunk */
+#define ETN_HIST_CALL_SECONDS 4    /* host-path call latency, submit to completion */
+#define ETN_HIST_REQS_PER_LAUNCH 5 /* host-path requests sharing one staged chunk */
+#define ETN_HIST_COUNT 6
+ETN_API int etn_get_histogram(int which, double *upper_bounds, int64_t *counts, int capacity,
+                              double *sum);
+ETN_API const char *etn_histogram_name(int which);
+ETN_API const char *etn_histogram_help(int which);
 
 /* ---- bench/test utility ---- */
 
@@ -232,6 +320,15 @@ ETN_API const char *etn_counter_name(int index);
  * counterpart (the reference has no benchmark for this path). */
 ETN_API int etn_fill_synthetic(uint64_t seed, int64_t row0, int64_t rows, int64_t D, int64_t ncols,
                        int64_t ld, int dtype, void *dev_out, void *stream);
+
+/* Raw copy ceiling of the calling thread's current device, measured the way the host path
+ * copies: `reps` x `bytes` H2D from host_in (directions & 1) and/or D2H into host_out
+ * (directions & 2) on two streams, wall-clock seconds into *seconds.  bench.py runs it on
+ * every rank at once to state end-to-end throughput as a fraction of what the box's copy
+ * path can do (profiles/r02_dma_matrix.txt).  Allocates `bytes` of device memory per
+ * direction for the duration of the call.  No reference counterpart. */
+ETN_API int etn_raw_copy_seconds(const void *host_in, void *host_out, size_t bytes, int reps,
+                                 int directions, double *seconds);
 
 #ifdef __cplusplus
 }

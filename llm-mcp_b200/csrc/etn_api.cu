@@ -1,40 +1,64 @@
-// etn_api.cu — the C-ABI of libembed_truncate_norm.so (declared in
-// include/embed_truncate_norm.h) and the host side above the kernels: argument checks,
-// kernel selection, and the end-to-end host-buffer path (chunked prefix-only H2D, kernel,
-// D2H, row-sharded over devices with one host thread and its own streams per device).
+// etn_api.cu — the device-pointer half of the C-ABI of libembed_truncate_norm.so (declared in
+// include/embed_truncate_norm.h): argument checks, kernel selection, metrics, the entry
+// point that stages through the built-in array.  The host-buffer runtime (persistent
+// per-device workers, chunked prefix-only H2D, kernel, D2H, coalescing, row sharding) is
+// etn_host.cu.
 //
 // Reference behaviour being replaced: truncateEmbeddings, core/internal/api/handlers.go:2062-2078,
 // called at handlers.go:1891-1893.  No torch, no NCCL, no CPU compute fallback: if the
 // CUDA runtime reports an error the caller gets its code.
 #include "../../include/embed_truncate_norm.h"
+#include "etn_internal.h"
 #include "etn_kernels.cuh"
 
 #include <algorithm>
+#include <cmath>
 #include <cstdlib>
 #include <atomic>
 #include <mutex>
-#include <thread>
 #include <vector>
 
 namespace {
 
 using namespace etn;
+using etn_rt::aligned_to;
+using etn_rt::count;
+using etn_rt::finish;
 
-inline bool aligned_to(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
-
-// ---------------------------------------------------------------- counters ----
+// ---------------------------------------------------------------- metrics ----
 // Cumulative, process-wide; the Go side exports them next to the embedding collectors of
 // core/internal/metrics/metrics.go:9-26.  Order = ETN_CTR_* in the header.
 std::atomic<int64_t> g_ctr[ETN_CTR_COUNT];
-inline void count(int i, int64_t v = 1) { g_ctr[i].fetch_add(v, std::memory_order_relaxed); }
 inline int counted_launch(cudaError_t e) {
   if (e == cudaSuccess) count(ETN_CTR_KERNEL_LAUNCHES);
   return (int)e;
 }
-inline int finish(int rc) {
-  if (rc != 0) count(ETN_CTR_ERRORS);
-  return rc;
-}
+
+// Fixed-bucket histograms in the shape of prometheus.HistogramOpts (metrics.go:18-26 is the
+// one to sit beside): upper bounds, per-bucket counts (not cumulative here), sum of samples.
+constexpr int kMaxBuckets = 16;
+struct Hist {
+  const char* name;
+  const char* help;
+  int n;                                    // finite upper bounds; bucket n is +Inf
+  double le[kMaxBuckets];
+  std::atomic<int64_t> cnt[kMaxBuckets + 1];
+  std::atomic<int64_t> sum_fixed;           // sum in units of 2^-30 (atomic add on integers)
+};
+Hist g_hist[ETN_HIST_COUNT] = {
+    {"llmcore_embed_gpu_batch_rows", "Rows per host-path call", 11,
+     {1, 4, 16, 64, 256, 1024, 4096, 16384, 65536, 262144, 1048576}, {}, {}},
+    {"llmcore_embed_gpu_kernel_seconds", "Kernel time per staged chunk (CUDA events)", 12,
+     {5e-6, 1e-5, 2e-5, 5e-5, 1e-4, 2e-4, 5e-4, 1e-3, 2e-3, 5e-3, 1e-2, 0.1}, {}, {}},
+    {"llmcore_embed_gpu_h2d_seconds", "Host-to-device copy time per staged chunk (CUDA events)", 12,
+     {5e-6, 1e-5, 2e-5, 5e-5, 1e-4, 2e-4, 5e-4, 1e-3, 2e-3, 5e-3, 1e-2, 0.1}, {}, {}},
+    {"llmcore_embed_gpu_d2h_seconds", "Device-to-host copy time per staged chunk (CUDA events)", 12,
+     {5e-6, 1e-5, 2e-5, 5e-5, 1e-4, 2e-4, 5e-4, 1e-3, 2e-3, 5e-3, 1e-2, 0.1}, {}, {}},
+    {"llmcore_embed_gpu_call_seconds", "Host-path call latency, submit to completion", 12,
+     {5e-5, 1e-4, 2e-4, 5e-4, 1e-3, 2e-3, 5e-3, 1e-2, 2e-2, 5e-2, 0.1, 1.0}, {}, {}},
+    {"llmcore_embed_gpu_requests_per_launch", "Host-path requests sharing one staged chunk (coalescing)", 8,
+     {1, 2, 4, 8, 16, 32, 64, 128}, {}, {}},
+};
 
 // ------------------------------------------------------------ device info ----
 struct DeviceInfo {
@@ -100,9 +124,9 @@ int launch_kernel(void (*kern)(KArgs...), int grid, cudaStream_t s, Args... args
 }
 
 // MINB = resident blocks per SM the register allocation is held to.
-template <typename T, int VB, int NV, int R, int L, int MODE, int MINB>
+template <typename T, int VB, int NV, int R, int L, int MODE, int MINB, int ALIAS>
 int launch_reg(const void* in, void* out, int64_t batch, int64_t in_pitch, int nvec, int waves, cudaStream_t s) {
-  auto kern = rows_reg_kernel<T, VB, NV, R, L, MODE, MINB, VB == 32 ? 1 : 0>;
+  auto kern = rows_reg_kernel<T, VB, NV, R, L, MODE, MINB, VB == 32 ? 1 : 0, ALIAS>;
   int grid = 0;
   const int64_t rows_per_block = (int64_t)kWarpsPerBlock * R * (32 / L);
   if (int rc = grid_for(kern, (batch + rows_per_block - 1) / rows_per_block, waves, &grid)) return rc;
@@ -187,16 +211,16 @@ int launch_bulk(const void* in, void* out, int64_t batch, int64_t in_pitch, int 
 
 template <typename T, int MODE>
 int launch_general(const void* in, void* out, int64_t batch, int64_t D, int64_t k,
-                   const int32_t* k_per_row, const int64_t* out_offsets, cudaStream_t s) {
+                   const int32_t* k_per_row, const int64_t* out_offsets, const int64_t* in_offsets, cudaStream_t s) {
   auto kern = rows_general_kernel<T, MODE>;
   int grid = 0;
   if (int rc = grid_for(kern, (batch + kWarpsPerBlock - 1) / kWarpsPerBlock, 0, &grid)) return rc;
-  return launch_kernel(kern, grid, s, (const T*)in, (T*)out, batch, D, k, k_per_row, out_offsets);
+  return launch_kernel(kern, grid, s, (const T*)in, (T*)out, batch, D, k, k_per_row, out_offsets, in_offsets);
 }
 
 template <typename T, int MODE>
 int launch_ring(const void* in, void* out, int64_t batch, int64_t D, int64_t k_dense, const int32_t* k_per_row,
-                const int64_t* out_offsets, cudaStream_t s);
+                const int64_t* out_offsets, const int64_t* in_offsets, cudaStream_t s);
 
 // Dense rows.  Kernel choice by prefix size and alignment:
 //   16-byte tileable, float64 renorm, 512 B - 8 KiB:  rows_bulk (bulk-async ring)
@@ -206,7 +230,8 @@ int launch_ring(const void* in, void* out, int64_t batch, int64_t D, int64_t k_d
 //   16-byte aligned input rows, odd k, <= 8 KiB:      rows_ring (staged rounded up, element-wise)
 //   anything else:                                    rows_general
 // Truncation moves bytes, so one instantiation (T = float) serves both element types.
-template <typename T, int MODE>
+// ALIAS = 1 (out == in): the register kernels load through the coherent path (no ld.global.nc).
+template <typename T, int MODE, int ALIAS>
 int launch_dense(const void* in, void* out, int64_t batch, int64_t D, int64_t kk, cudaStream_t s) {
   using TT = typename std::conditional<MODE == kModeTruncate, float, T>::type;
   // float64 renorm carries the compensated sum and the double-double scale: more registers
@@ -241,47 +266,50 @@ int launch_dense(const void* in, void* out, int64_t batch, int64_t D, int64_t kk
     const int nv = (nvec + 31) / 32;
     // short rows: 8 or 16 lanes per row, so a warp finishes 4 or 2 rows per reduction
     constexpr int RS = heavy ? 2 : 8, MBS = heavy ? 4 : 2;
-    if (nvec <= 8)  return launch_reg<TT, 32, 1, RS, 8, MODE, MBS>(in, out, batch, in_pitch, nvec, W, s);
-    if (nvec <= 16) return launch_reg<TT, 32, 1, RS, 16, MODE, MBS>(in, out, batch, in_pitch, nvec, W, s);
-    if (nv <= 1) return launch_reg<TT, 32, 1, R1, 32, MODE, MB>(in, out, batch, in_pitch, nvec, W, s);
-    if (nv <= 2) return launch_reg<TT, 32, 2, R2, 32, MODE, MB>(in, out, batch, in_pitch, nvec, W, s);
-    if (nv <= 4) return launch_reg<TT, 32, 4, 1, 32, MODE, MB4>(in, out, batch, in_pitch, nvec, W, s);
+    if (nvec <= 8)  return launch_reg<TT, 32, 1, RS, 8, MODE, MBS, ALIAS>(in, out, batch, in_pitch, nvec, W, s);
+    if (nvec <= 16) return launch_reg<TT, 32, 1, RS, 16, MODE, MBS, ALIAS>(in, out, batch, in_pitch, nvec, W, s);
+    if (nv <= 1) return launch_reg<TT, 32, 1, R1, 32, MODE, MB, ALIAS>(in, out, batch, in_pitch, nvec, W, s);
+    if (nv <= 2) return launch_reg<TT, 32, 2, R2, 32, MODE, MB, ALIAS>(in, out, batch, in_pitch, nvec, W, s);
+    if (nv <= 4) return launch_reg<TT, 32, 4, 1, 32, MODE, MB4, ALIAS>(in, out, batch, in_pitch, nvec, W, s);
     // 4-8 KiB rows: float32 renorm does as well through the bulk ring (6.79 vs 6.65 TB/s)
     if constexpr (MODE == kModeRenorm && !heavy)
       return launch_bulk<T, 16, 2, MODE>(in, out, batch, in_pitch, (int)(k_bytes / 16), 4, s);
-    return launch_reg<TT, 32, 8, 1, 32, MODE, MB8>(in, out, batch, in_pitch, nvec, W, s);
+    return launch_reg<TT, 32, 8, 1, 32, MODE, MB8, ALIAS>(in, out, batch, in_pitch, nvec, W, s);
   }
   if (aligned_to(in, 16) && aligned_to(out, 16) && in_pitch % 16 == 0 && k_bytes % 16 == 0 &&
       k_bytes <= 16 * 512) {
     const int nvec = (int)(k_bytes / 16);
     const int nv = (nvec + 31) / 32;
-    if (nvec <= 8)  return launch_reg<TT, 16, 1, 2 * R1, 8, MODE, MB>(in, out, batch, in_pitch, nvec, W, s);
-    if (nvec <= 16) return launch_reg<TT, 16, 1, 2 * R1, 16, MODE, MB>(in, out, batch, in_pitch, nvec, W, s);
-    if (nv <= 1) return launch_reg<TT, 16, 1, 2 * R1, 32, MODE, MB>(in, out, batch, in_pitch, nvec, W, s);
-    if (nv <= 2) return launch_reg<TT, 16, 2, R1, 32, MODE, MB>(in, out, batch, in_pitch, nvec, W, s);
-    if (nv <= 4) return launch_reg<TT, 16, 4, R2, 32, MODE, MB>(in, out, batch, in_pitch, nvec, W, s);
-    if (nv <= 8) return launch_reg<TT, 16, 8, 1, 32, MODE, MB4>(in, out, batch, in_pitch, nvec, W, s);
-    return launch_reg<TT, 16, 16, 1, 32, MODE, MB8>(in, out, batch, in_pitch, nvec, W, s);
+    if (nvec <= 8)  return launch_reg<TT, 16, 1, 2 * R1, 8, MODE, MB, ALIAS>(in, out, batch, in_pitch, nvec, W, s);
+    if (nvec <= 16) return launch_reg<TT, 16, 1, 2 * R1, 16, MODE, MB, ALIAS>(in, out, batch, in_pitch, nvec, W, s);
+    if (nv <= 1) return launch_reg<TT, 16, 1, 2 * R1, 32, MODE, MB, ALIAS>(in, out, batch, in_pitch, nvec, W, s);
+    if (nv <= 2) return launch_reg<TT, 16, 2, R1, 32, MODE, MB, ALIAS>(in, out, batch, in_pitch, nvec, W, s);
+    if (nv <= 4) return launch_reg<TT, 16, 4, R2, 32, MODE, MB, ALIAS>(in, out, batch, in_pitch, nvec, W, s);
+    if (nv <= 8) return launch_reg<TT, 16, 8, 1, 32, MODE, MB4, ALIAS>(in, out, batch, in_pitch, nvec, W, s);
+    return launch_reg<TT, 16, 16, 1, 32, MODE, MB8, ALIAS>(in, out, batch, in_pitch, nvec, W, s);
   }
   // prefix not 16-byte tileable (odd k) but 16-byte aligned input rows: staged through the ring
   if (aligned_to(in, 16) && in_pitch % 16 == 0 && k_bytes <= 8192 - 16)
-    return launch_ring<T, MODE>(in, out, batch, D, kk, nullptr, nullptr, s);
-  return launch_general<T, MODE>(in, out, batch, D, kk, nullptr, nullptr, s);
+    return launch_ring<T, MODE>(in, out, batch, D, kk, nullptr, nullptr, nullptr, s);
+  return launch_general<T, MODE>(in, out, batch, D, kk, nullptr, nullptr, nullptr, s);
 }
 
 // Ragged rows: every row prefix is one bulk-async copy of its own length into a warp's
 // page-granular ring (rows_ring_kernel), so mixed k costs no padding traffic and short rows
 // still keep the ring full; rows that are not 16-byte tileable or exceed 8 KiB fall back
 // inside the kernel.
+// in_offsets != nullptr: the caller guarantees every row start is 16-byte aligned.
 template <typename T, int MODE>
 int launch_ring(const void* in, void* out, int64_t batch, int64_t D, int64_t k_dense, const int32_t* k_per_row,
-                const int64_t* out_offsets, cudaStream_t s) {
+                const int64_t* out_offsets, const int64_t* in_offsets, cudaStream_t s) {
   const int64_t in_pitch = D * (int64_t)sizeof(T);
-  if (!(aligned_to(in, 16) && in_pitch % 16 == 0))
-    return launch_general<T, MODE>(in, out, batch, D, k_dense, k_per_row, out_offsets, s);
+  if (!(aligned_to(in, 16) && (in_offsets || in_pitch % 16 == 0)))
+    return launch_general<T, MODE>(in, out, batch, D, k_dense, k_per_row, out_offsets, in_offsets, s);
   constexpr int NCW = 4;
   constexpr size_t smem = (size_t)NCW * 8192 + (size_t)NCW * 8 * 8 + (size_t)NCW * 8 * 3 * 4;
-  auto kern = rows_ring_kernel<T, NCW, MODE>;
+  // 16 pages per warp, register budget of 4 resident blocks (6 still fit), 4 rows per warp: tools/tune ring,
+  // profiles/r02_tune_ring.txt (config-5 mix 6.39 TB/s, 64 merged C1 requests 6.17 TB/s)
+  auto kern = rows_ring_kernel<T, NCW, MODE, 16, 4>;
   {
     static std::atomic<uint64_t> done{0};
     int dev = 0;
@@ -296,7 +324,7 @@ int launch_ring(const void* in, void* out, int64_t batch, int64_t D, int64_t k_d
   }
   int dev = 0, sms = 148;
   if (cudaGetDevice(&dev) == cudaSuccess) sm_count(dev, &sms);
-  const int rpw = (int)std::max<int64_t>(1, std::min<int64_t>(16, batch / ((int64_t)NCW * sms * 2)));
+  const int rpw = (int)std::max<int64_t>(1, std::min<int64_t>(4, batch / ((int64_t)NCW * sms * 2)));
   const int64_t rows_per_block = (int64_t)NCW * rpw;
   const int64_t blocks = std::min<int64_t>((batch + rows_per_block - 1) / rows_per_block, (int64_t)1 << 30);
   cudaLaunchConfig_t cfg = {};
@@ -310,13 +338,7 @@ int launch_ring(const void* in, void* out, int64_t batch, int64_t D, int64_t k_d
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
   return counted_launch(cudaLaunchKernelEx(&cfg, kern, (const char*)in, (char*)out, batch, in_pitch, rpw, D, k_dense,
-                                           k_per_row, out_offsets));
-}
-
-template <typename T, int MODE>
-int launch_ragged(const void* in, void* out, int64_t batch, int64_t D, const int32_t* k_per_row,
-                  const int64_t* out_offsets, cudaStream_t s) {
-  return launch_ring<T, MODE>(in, out, batch, D, 0, k_per_row, out_offsets, s);
+                                           k_per_row, out_offsets, in_offsets));
 }
 
 int check_dense(int64_t batch, int64_t D, int64_t k, int dtype, const void* in, const void* out) {
@@ -326,101 +348,62 @@ int check_dense(int64_t batch, int64_t D, int64_t k, int dtype, const void* in, 
   if (!in || !out) return ETN_ERR_NULL;
   const size_t es = dtype == ETN_F32 ? 4 : 8;
   if (!aligned_to(in, es) || !aligned_to(out, es)) return ETN_ERR_ALIGN;
+  if (in == out && k < D) return ETN_ERR_SHAPE;     // in place only when whole rows are kept
   return ETN_OK;
+}
+
+}  // namespace
+
+// ------------------------------------------------ shared with etn_host.cu ----
+namespace etn_rt {
+
+void count(int i, int64_t v) { g_ctr[i].fetch_add(v, std::memory_order_relaxed); }
+
+int finish(int rc) {
+  if (rc == ETN_ERR_JSON || rc == ETN_ERR_JSON_DUP || rc == ETN_ERR_TOO_LARGE || rc == ETN_ERR_NOT_INIT) count(ETN_CTR_FALLBACKS);
+  else if (rc != 0) count(ETN_CTR_ERRORS);
+  return rc;
+}
+
+void observe(int which, double v) {
+  if (which < 0 || which >= ETN_HIST_COUNT || !(v >= 0.0)) return;
+  Hist& h = g_hist[which];
+  int b = 0;
+  while (b < h.n && v > h.le[b]) ++b;
+  h.cnt[b].fetch_add(1, std::memory_order_relaxed);
+  h.sum_fixed.fetch_add((int64_t)std::llround(v * 1073741824.0), std::memory_order_relaxed);
 }
 
 int run_dense(int64_t batch, int64_t D, int64_t k, int dtype, int mode, const void* in, void* out,
               cudaStream_t s) {
   const int64_t kk = std::min(k, D);
+  if (in == out) {                                   // k >= D: whole rows, normalised where they lie
+    if (mode == ETN_TRUNCATE) return ETN_OK;         // copying a row onto itself
+    return dtype == ETN_F32 ? launch_dense<float, kModeRenorm, 1>(in, out, batch, D, kk, s)
+                            : launch_dense<double, kModeRenorm, 1>(in, out, batch, D, kk, s);
+  }
   if (mode == ETN_TRUNCATE) {
-    return dtype == ETN_F32 ? launch_dense<float, kModeTruncate>(in, out, batch, D, kk, s)
-                            : launch_dense<double, kModeTruncate>(in, out, batch, D, kk, s);
+    return dtype == ETN_F32 ? launch_dense<float, kModeTruncate, 0>(in, out, batch, D, kk, s)
+                            : launch_dense<double, kModeTruncate, 0>(in, out, batch, D, kk, s);
   }
-  return dtype == ETN_F32 ? launch_dense<float, kModeRenorm>(in, out, batch, D, kk, s)
-                          : launch_dense<double, kModeRenorm>(in, out, batch, D, kk, s);
+  return dtype == ETN_F32 ? launch_dense<float, kModeRenorm, 0>(in, out, batch, D, kk, s)
+                          : launch_dense<double, kModeRenorm, 0>(in, out, batch, D, kk, s);
 }
 
-// --------------------------------------------------------------- host path ----
-// Measured on the B200 box (profiles/r01_pcie_study.txt): DMA moves 55.6 GB/s H2D, 57.3 GB/s
-// D2H, 50 GB/s each way when both run; a prefix-only 2-D copy (4 KiB of every 16 KiB) is as
-// fast as a contiguous one; the kernels reading and writing pinned host memory directly
-// reach 40 GB/s each way.  Hence staged DMA, both directions kept busy at once.
-constexpr int kSlots = 4;                          // chunks in flight per device
-constexpr size_t kSlotBytes = 64u << 20;           // staging per slot (prefix bytes)
-constexpr int64_t kMinChunkBytes = 512 << 10;      // below this a chunk is all submission latency
-
-struct DevCtx {
-  int dev = -1;
-  cudaStream_t stream[kSlots] = {};
-  void* stage[kSlots] = {};
-  std::mutex mu;                                   // one host call at a time per device
-};
-
-std::mutex g_init_mu;
-std::vector<DevCtx*> g_ctx;                        // guarded by g_init_mu for (de)construction
-std::atomic<int> g_ndev{0};
-
-void destroy_ctx(DevCtx* c) {
-  if (!c) return;
-  if (cudaSetDevice(c->dev) == cudaSuccess) {
-    for (int i = 0; i < kSlots; ++i) {
-      if (c->stream[i]) { cudaStreamSynchronize(c->stream[i]); cudaStreamDestroy(c->stream[i]); }
-      if (c->stage[i]) cudaFree(c->stage[i]);
-    }
-  }
-  delete c;
+int run_rows(int64_t batch, int64_t D, const int32_t* k_per_row, const int64_t* out_offsets,
+             const int64_t* in_offsets, int dtype, int mode, const void* in, void* out, cudaStream_t s) {
+  if (mode == ETN_TRUNCATE)
+    return dtype == ETN_F32
+               ? launch_ring<float, kModeTruncate>(in, out, batch, D, 0, k_per_row, out_offsets, in_offsets, s)
+               : launch_ring<double, kModeTruncate>(in, out, batch, D, 0, k_per_row, out_offsets, in_offsets, s);
+  return dtype == ETN_F32
+             ? launch_ring<float, kModeRenorm>(in, out, batch, D, 0, k_per_row, out_offsets, in_offsets, s)
+             : launch_ring<double, kModeRenorm>(in, out, batch, D, 0, k_per_row, out_offsets, in_offsets, s);
 }
 
-// Processes rows [0, rows) of one device's block.  host_in/host_out already point at the
-// block.  Every chunk runs H2D -> kernel (in place on the dense staging tile) -> D2H on its
-// slot's stream; the slots keep both copy engines and the SMs busy at once.
-int run_block(DevCtx* c, int64_t rows, int64_t kk, int dtype, int mode, const char* host_in,
-              int64_t in_pitch, char* host_out) {
-  std::lock_guard<std::mutex> lock(c->mu);
-  cudaError_t e = cudaSetDevice(c->dev);
-  if (e != cudaSuccess) return (int)e;
-  const int64_t es = dtype == ETN_F32 ? 4 : 8;
-  const int64_t k_bytes = kk * es;
-  int64_t chunk_rows = (int64_t)(kSlotBytes / (size_t)k_bytes);
-  if (chunk_rows < 1) return ETN_ERR_SHAPE;        // one row prefix larger than a slot
-  // a request-sized batch is cut into ~2*kSlots chunks so its D2H overlaps its own H2D.
-  // (Measured, profiles/r01_pcie_study.txt: for an 8 MiB request this buys 10-15 %; copies of
-  // a few MiB in opposite directions overlap far less than the GiB-sized ones do.)
-  const int64_t split = (rows + 2 * kSlots - 1) / (2 * kSlots);
-  const int64_t floor_rows = std::max<int64_t>(1, kMinChunkBytes / k_bytes);
-  chunk_rows = std::min(chunk_rows, std::max(split, floor_rows));
-  int rc = 0;
-  int64_t done = 0;
-  for (int64_t ci = 0; done < rows && rc == 0; ++ci) {
-    const int slot = (int)(ci % kSlots);
-    cudaStream_t s = c->stream[slot];
-    const int64_t n = std::min(chunk_rows, rows - done);
-    const char* src = host_in + done * in_pitch;
-    if (in_pitch == k_bytes) {
-      e = cudaMemcpyAsync(c->stage[slot], src, (size_t)(n * k_bytes), cudaMemcpyHostToDevice, s);
-    } else {
-      e = cudaMemcpy2DAsync(c->stage[slot], (size_t)k_bytes, src, (size_t)in_pitch, (size_t)k_bytes,
-                            (size_t)n, cudaMemcpyHostToDevice, s);
-    }
-    if (e != cudaSuccess) { rc = (int)e; break; }
-    // staging is dense [n x kk]: D == kk, so renormalising in place is allowed
-    if (mode == ETN_TRUNCATE_RENORM) {
-      rc = run_dense(n, kk, kk, dtype, mode, c->stage[slot], c->stage[slot], s);
-      if (rc) break;
-    }
-    e = cudaMemcpyAsync(host_out + done * k_bytes, c->stage[slot], (size_t)(n * k_bytes),
-                        cudaMemcpyDeviceToHost, s);
-    if (e != cudaSuccess) { rc = (int)e; break; }
-    done += n;
-  }
-  for (int i = 0; i < kSlots; ++i) {
-    e = cudaStreamSynchronize(c->stream[i]);
-    if (e != cudaSuccess && rc == 0) rc = (int)e;
-  }
-  return rc;
-}
+}  // namespace etn_rt
 
-}  // namespace
+using etn_rt::run_dense;
 
 // ------------------------------------------------- built-in staging array ----
 // Device staging for embed_truncate_norm_host_static: reserved in the module image, so it
@@ -445,7 +428,7 @@ const char* etn_strerror(int code) {
   switch (code) {
     case ETN_OK: return "ok";
     case ETN_ERR_NULL: return "null pointer";
-    case ETN_ERR_SHAPE: return "bad shape (batch < 0, D <= 0, k <= 0, bad pitch or offsets)";
+    case ETN_ERR_SHAPE: return "bad shape (batch < 0, D <= 0, k <= 0, bad pitch or offsets, or out == in with k < D)";
     case ETN_ERR_ENUM: return "unknown dtype or mode";
     case ETN_ERR_ALIGN: return "pointer not aligned to the element size";
     case ETN_ERR_NOT_INIT: return "etn_init has not been called";
@@ -453,6 +436,7 @@ const char* etn_strerror(int code) {
     case ETN_ERR_JSON: return "malformed JSON, non-finite value or number outside float64";
     case ETN_ERR_JSON_DUP: return "duplicate \"data\" or \"embedding\" key";
     case ETN_ERR_TOO_LARGE: return "batch does not fit the built-in staging array (ETN_STATIC_STAGE_BYTES)";
+    case ETN_ERR_TICKET: return "unknown or already waited-for ticket";
     default: break;
   }
   if (code > 0) return cudaGetErrorString((cudaError_t)code);
@@ -475,9 +459,8 @@ int embed_truncate(int64_t batch, int64_t D, int64_t k, int dtype, const void* i
   return finish(run_dense(batch, D, k, dtype, ETN_TRUNCATE, in, out, (cudaStream_t)stream));
 }
 
-int embed_truncate_norm_ragged(int64_t batch, int64_t D, const int32_t* k_per_row,
-                               const int64_t* out_offsets, int dtype, int mode, const void* in,
-                               void* out, void* stream) {
+static int check_rows(int64_t batch, int64_t D, const int32_t* k_per_row, const int64_t* out_offsets,
+                      int dtype, int mode, const void* in, const void* out) {
   if ((dtype != ETN_F32 && dtype != ETN_F64) || (mode != ETN_TRUNCATE && mode != ETN_TRUNCATE_RENORM))
     return ETN_ERR_ENUM;
   if (batch < 0 || D <= 0) return ETN_ERR_SHAPE;
@@ -487,126 +470,33 @@ int embed_truncate_norm_ragged(int64_t batch, int64_t D, const int32_t* k_per_ro
   if (!aligned_to(in, es) || !aligned_to(out, es) || !aligned_to(k_per_row, 4) ||
       !aligned_to(out_offsets, 8))
     return ETN_ERR_ALIGN;
-  cudaStream_t s = (cudaStream_t)stream;
-  count(ETN_CTR_DEVICE_CALLS); count(ETN_CTR_DEVICE_ROWS, batch);
-  if (mode == ETN_TRUNCATE)
-    return finish(dtype == ETN_F32 ? launch_ragged<float, kModeTruncate>(in, out, batch, D, k_per_row, out_offsets, s)
-                                   : launch_ragged<double, kModeTruncate>(in, out, batch, D, k_per_row, out_offsets, s));
-  return finish(dtype == ETN_F32 ? launch_ragged<float, kModeRenorm>(in, out, batch, D, k_per_row, out_offsets, s)
-                                 : launch_ragged<double, kModeRenorm>(in, out, batch, D, k_per_row, out_offsets, s));
-}
-
-int etn_init(const int* device_ids, int n_devices) {
-  std::lock_guard<std::mutex> lock(g_init_mu);
-  if (!g_ctx.empty()) return ETN_OK;
-  int visible = 0;
-  cudaError_t e = cudaGetDeviceCount(&visible);
-  if (e != cudaSuccess) return (int)e;
-  std::vector<int> ids;
-  if (!device_ids || n_devices <= 0) {
-    for (int i = 0; i < visible; ++i) ids.push_back(i);
-  } else {
-    for (int i = 0; i < n_devices; ++i) {
-      if (device_ids[i] < 0 || device_ids[i] >= visible) return ETN_ERR_DEVICE;
-      ids.push_back(device_ids[i]);
-    }
-  }
-  if (ids.empty()) return ETN_ERR_DEVICE;
-  int prev = 0;
-  cudaGetDevice(&prev);
-  std::vector<DevCtx*> made;
-  int rc = 0;
-  for (int id : ids) {
-    DevCtx* c = new DevCtx();
-    c->dev = id;
-    made.push_back(c);
-    if ((e = cudaSetDevice(id)) != cudaSuccess) { rc = (int)e; break; }
-    for (int i = 0; i < kSlots && rc == 0; ++i) {
-      if ((e = cudaStreamCreateWithFlags(&c->stream[i], cudaStreamNonBlocking)) != cudaSuccess) rc = (int)e;
-      else if ((e = cudaMalloc(&c->stage[i], kSlotBytes)) != cudaSuccess) rc = (int)e;
-    }
-    if (rc) break;
-  }
-  cudaSetDevice(prev);
-  if (rc) { for (DevCtx* c : made) destroy_ctx(c); return rc; }
-  g_ctx.swap(made);
-  g_ndev.store((int)g_ctx.size());
   return ETN_OK;
 }
 
-void etn_shutdown(void) {
-  std::lock_guard<std::mutex> lock(g_init_mu);
-  int prev = 0;
-  const bool have_prev = cudaGetDevice(&prev) == cudaSuccess;
-  for (DevCtx* c : g_ctx) destroy_ctx(c);
-  g_ctx.clear();
-  g_ndev.store(0);
-  if (have_prev) cudaSetDevice(prev);
-}
-
-int etn_device_count(void) { return g_ndev.load(); }
-
-void* etn_alloc_pinned(size_t bytes) {
-  void* p = nullptr;
-  if (bytes == 0) return nullptr;
-  if (cudaHostAlloc(&p, bytes, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return nullptr; }
-  return p;
-}
-
-void etn_free_pinned(void* p) {
-  if (p) cudaFreeHost(p);
-}
-
-int embed_truncate_norm_host(int64_t batch, int64_t D, int64_t k, int dtype, int mode,
-                             const void* host_in, int64_t in_pitch_bytes, void* host_out,
-                             int n_devices) {
-  if ((dtype != ETN_F32 && dtype != ETN_F64) || (mode != ETN_TRUNCATE && mode != ETN_TRUNCATE_RENORM))
-    return ETN_ERR_ENUM;
-  if (batch < 0 || D <= 0 || k <= 0) return ETN_ERR_SHAPE;
-  const int64_t es = dtype == ETN_F32 ? 4 : 8;
-  if (in_pitch_bytes == 0) in_pitch_bytes = D * es;
-  if (in_pitch_bytes < D * es || in_pitch_bytes % es != 0) return ETN_ERR_SHAPE;
-  if (n_devices < 0) return ETN_ERR_DEVICE;
+int embed_truncate_norm_ragged(int64_t batch, int64_t D, const int32_t* k_per_row,
+                               const int64_t* out_offsets, int dtype, int mode, const void* in,
+                               void* out, void* stream) {
+  if (int rc = check_rows(batch, D, k_per_row, out_offsets, dtype, mode, in, out)) return rc;
   if (batch == 0) return ETN_OK;
-  if (!host_in || !host_out) return ETN_ERR_NULL;
-  if (!aligned_to(host_in, (size_t)es) || !aligned_to(host_out, (size_t)es)) return ETN_ERR_ALIGN;
+  count(ETN_CTR_DEVICE_CALLS); count(ETN_CTR_DEVICE_ROWS, batch);
+  return finish(etn_rt::run_rows(batch, D, k_per_row, out_offsets, nullptr, dtype, mode, in, out,
+                                 (cudaStream_t)stream));
+}
 
-  std::vector<DevCtx*> ctx;
-  {
-    std::lock_guard<std::mutex> lock(g_init_mu);
-    ctx = g_ctx;
-  }
-  if (ctx.empty()) return ETN_ERR_NOT_INIT;
-  if (n_devices == 0) n_devices = (int)ctx.size();
-  if (n_devices > (int)ctx.size()) return ETN_ERR_DEVICE;
-  n_devices = (int)std::min<int64_t>(n_devices, batch);
-
-  const int64_t kk = std::min(k, D);
-  const char* hin = (const char*)host_in;
-  char* hout = (char*)host_out;
-  // contiguous row blocks: device g gets rows [g*per, min(batch, (g+1)*per))
-  const int64_t per = (batch + n_devices - 1) / n_devices;
-  int prev = 0;
-  const bool have_prev = cudaGetDevice(&prev) == cudaSuccess;
-  std::vector<int> rcs(n_devices, 0);
-  auto work = [&](int g) {
-    const int64_t r0 = (int64_t)g * per, r1 = std::min(batch, r0 + per);
-    if (r1 <= r0) return;
-    rcs[g] = run_block(ctx[g], r1 - r0, kk, dtype, mode, hin + r0 * in_pitch_bytes,
-                       in_pitch_bytes, hout + r0 * kk * es);
-  };
-  if (n_devices == 1) {
-    work(0);
-  } else {
-    std::vector<std::thread> th;
-    for (int g = 0; g < n_devices; ++g) th.emplace_back(work, g);
-    for (auto& t : th) t.join();
-  }
-  if (have_prev) cudaSetDevice(prev);
-  count(ETN_CTR_HOST_CALLS); count(ETN_CTR_HOST_ROWS, batch);
-  for (int rc : rcs) if (rc) return finish(rc);
-  count(ETN_CTR_H2D_BYTES, batch * kk * es); count(ETN_CTR_D2H_BYTES, batch * kk * es);
-  return ETN_OK;
+int embed_truncate_norm_gather(int64_t batch, const int64_t* in_offsets, const int32_t* k_per_row,
+                               const int64_t* out_offsets, int dtype, int mode, const void* in_base,
+                               void* out_base, void* stream) {
+  if (int rc = check_rows(batch, 1, k_per_row, out_offsets, dtype, mode, in_base, out_base)) return rc;
+  if (batch == 0) return ETN_OK;
+  if (!in_offsets) return ETN_ERR_NULL;
+  if (!aligned_to(in_offsets, 8)) return ETN_ERR_ALIGN;
+  // rows reach the page ring by bulk-async copies, which need 16-byte aligned sources: the
+  // base is checked here, the offsets are the caller's promise (element offsets that are
+  // multiples of 16 / element size)
+  if (!aligned_to(in_base, 16)) return ETN_ERR_ALIGN;
+  count(ETN_CTR_DEVICE_CALLS); count(ETN_CTR_DEVICE_ROWS, batch);
+  return finish(etn_rt::run_rows(batch, INT64_MAX / 16, k_per_row, out_offsets, in_offsets, dtype, mode,
+                                 in_base, out_base, (cudaStream_t)stream));
 }
 
 int embed_truncate_norm_host_static(int64_t batch, int64_t D, int64_t k, int dtype, int mode,
@@ -624,21 +514,23 @@ int embed_truncate_norm_host_static(int64_t batch, int64_t D, int64_t k, int dty
   const int64_t kk = std::min(k, D);
   const int64_t k_bytes = kk * es;
   if (k_bytes > (int64_t)ETN_STATIC_STAGE_BYTES || batch > (int64_t)ETN_STATIC_STAGE_BYTES / k_bytes)
-    return ETN_ERR_TOO_LARGE;
+    return finish(ETN_ERR_TOO_LARGE);
 
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
-  if (e != cudaSuccess) return (int)e;
-  if (dev < 0 || dev >= kMaxDevices) return ETN_ERR_DEVICE;
+  if (e != cudaSuccess) return finish((int)e);
+  if (dev < 0 || dev >= kMaxDevices) return finish(ETN_ERR_DEVICE);
   StaticStage& st = g_static[dev];
   // Held until the stream has drained: every call on this device uses the same array.
   std::lock_guard<std::mutex> lock(st.mu);
   if (!st.ptr) {                                    // first call on this device: set-up
     void* p = nullptr;
     e = cudaGetSymbolAddress(&p, g_static_stage);
-    if (e != cudaSuccess) return (int)e;
+    if (e != cudaSuccess) return finish((int)e);
     st.ptr = p;
   }
+  count(ETN_CTR_HOST_CALLS); count(ETN_CTR_HOST_ROWS, batch);
+  etn_rt::observe(ETN_HIST_BATCH_ROWS, (double)batch);
   cudaStream_t s = (cudaStream_t)stream;
   const size_t bytes = (size_t)(batch * k_bytes);
   // Nothing in the array has to start at zero: the copy below overwrites exactly the
@@ -649,7 +541,7 @@ int embed_truncate_norm_host_static(int64_t batch, int64_t D, int64_t k, int dty
     e = cudaMemcpy2DAsync(st.ptr, (size_t)k_bytes, host_in, (size_t)in_pitch_bytes, (size_t)k_bytes,
                           (size_t)batch, cudaMemcpyHostToDevice, s);
   }
-  if (e != cudaSuccess) return (int)e;
+  if (e != cudaSuccess) return finish((int)e);
   int rc = 0;
   if (mode == ETN_TRUNCATE_RENORM) rc = run_dense(batch, kk, kk, dtype, mode, st.ptr, st.ptr, s);
   if (rc == 0) {
@@ -658,7 +550,8 @@ int embed_truncate_norm_host_static(int64_t batch, int64_t D, int64_t k, int dty
   }
   e = cudaStreamSynchronize(s);
   if (e != cudaSuccess && rc == 0) rc = (int)e;
-  return rc;
+  if (rc == 0) { count(ETN_CTR_H2D_BYTES, (int64_t)bytes); count(ETN_CTR_D2H_BYTES, (int64_t)bytes); }
+  return finish(rc);
 }
 
 int etn_get_counters(int64_t* out, int capacity) {
@@ -673,8 +566,36 @@ const char* etn_counter_name(int i) {
       "llmcore_embed_gpu_device_calls_total", "llmcore_embed_gpu_device_rows_total",
       "llmcore_embed_gpu_kernel_launches_total", "llmcore_embed_gpu_host_calls_total",
       "llmcore_embed_gpu_host_rows_total", "llmcore_embed_gpu_h2d_bytes_total",
-      "llmcore_embed_gpu_d2h_bytes_total", "llmcore_embed_gpu_errors_total"};
+      "llmcore_embed_gpu_d2h_bytes_total", "llmcore_embed_gpu_errors_total",
+      "llmcore_embed_gpu_fallback_total", "llmcore_embed_gpu_coalesced_requests_total"};
   return (i >= 0 && i < ETN_CTR_COUNT) ? names[i] : "";
+}
+
+void etn_note_fallback(int64_t vectors) {
+  if (vectors > 0) count(ETN_CTR_FALLBACKS, vectors);
+}
+
+int etn_get_histogram(int which, double* upper_bounds, int64_t* counts, int capacity, double* sum) {
+  if (which < 0 || which >= ETN_HIST_COUNT) return ETN_ERR_ENUM;
+  const Hist& h = g_hist[which];
+  const int n = h.n + 1;
+  if (!upper_bounds && !counts) return n;
+  if (!upper_bounds || !counts) return ETN_ERR_NULL;
+  if (capacity < n) return ETN_ERR_SHAPE;
+  for (int i = 0; i < n; ++i) {
+    upper_bounds[i] = i < h.n ? h.le[i] : INFINITY;
+    counts[i] = h.cnt[i].load(std::memory_order_relaxed);
+  }
+  if (sum) *sum = (double)h.sum_fixed.load(std::memory_order_relaxed) / 1073741824.0;
+  return n;
+}
+
+const char* etn_histogram_name(int which) {
+  return (which >= 0 && which < ETN_HIST_COUNT) ? g_hist[which].name : "";
+}
+
+const char* etn_histogram_help(int which) {
+  return (which >= 0 && which < ETN_HIST_COUNT) ? g_hist[which].help : "";
 }
 
 int etn_fill_synthetic(uint64_t seed, int64_t row0, int64_t rows, int64_t D, int64_t ncols,

@@ -141,9 +141,22 @@ __device__ __forceinline__ bool ss_in_range(double ss) {
 // ---------------------------------------------------------- vector access ----
 // Input is read exactly once and output written exactly once: no L1 allocation; with the
 // 256-bit forms (sm_100) also L2::evict_first when HINT == 1.
-template <int VB, int HINT>
+// ALIAS == 0: loads go through the non-coherent path (ld.global.nc), which PTX allows only for
+// memory no thread writes while the kernel runs — true whenever `out` does not overlap `in`.
+// ALIAS == 1 (out == in, rows normalised in place): ordinary coherent loads, so that reading a
+// row and then overwriting it is defined behaviour.
+template <int VB, int HINT, int ALIAS = 0>
 __device__ __forceinline__ void ld_vec(uint32_t* w, const void* p) {
-  if constexpr (VB == 16) {
+  if constexpr (ALIAS == 1) {
+    if constexpr (VB == 16) {
+      asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                   : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "l"(p) : "memory");
+    } else {
+      asm volatile("ld.global.L1::no_allocate.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                   : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
+                   : "l"(p) : "memory");
+    }
+  } else if constexpr (VB == 16) {
     asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
                  : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "l"(p));
   } else if constexpr (HINT == 1) {
@@ -341,9 +354,11 @@ __device__ __forceinline__ void general_row(const T* x, T* y, int64_t kr, int la
 // before anything is consumed (R*NV*VB*32 bytes per warp in flight).  Requires VB-aligned
 // rows on both sides; nvec = VB-byte vectors per prefix (<= NV*L).  L < 32 keeps short rows
 // (<= 512 B) from paying a whole warp's reduction and scale computation each.
-template <typename T, int VB, int NV, int R, int L, int MODE, int MINB, int HINT>
+// (in/out carry no __restrict__ anywhere in this file: every global access is explicit inline
+// PTX, so the qualifier buys nothing, and out == in is a legal call for k >= D.)
+template <typename T, int VB, int NV, int R, int L, int MODE, int MINB, int HINT, int ALIAS = 0>
 __global__ void __launch_bounds__(kThreads, MINB)
-rows_reg_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t batch,
+rows_reg_kernel(const char* in, char* out, int64_t batch,
                 int64_t in_pitch /*bytes*/, int nvec_dense) {
   pdl_prologue();
   constexpr int W = VB / 4, NW = NV * W;
@@ -368,7 +383,7 @@ rows_reg_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t bat
       for (int j = 0; j < NV; ++j) {
         const int idx = j * L + sl;
         if (idx < nvec[r]) {
-          ld_vec<VB, HINT>(&w[r][j * W], src + (int64_t)idx * VB);
+          ld_vec<VB, HINT, ALIAS>(&w[r][j * W], src + (int64_t)idx * VB);
         } else {
 #pragma unroll
           for (int q = 0; q < W; ++q) w[r][j * W + q] = 0u;
@@ -450,7 +465,7 @@ __device__ __forceinline__ void bulk_load_row(uint32_t dst, const void* src, uin
 
 template <typename T, int NV16, int S, int NCW, int MODE>
 __global__ void __launch_bounds__(NCW * 32, (NV16 > 12 ? ((sizeof(T) == 4 && MODE == kModeRenorm) ? 2 : 3) : 4))
-rows_bulk_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t batch,
+rows_bulk_kernel(const char* in, char* out, int64_t batch,
                  int64_t in_pitch /*bytes*/, int nvec16, int rows_per_warp) {
   constexpr int NW = NV16 * 4;
   constexpr int SLOT = NV16 * 32 * 16;                 // bytes per ring slot
@@ -543,12 +558,13 @@ rows_bulk_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t ba
 // bytes is staged rounded up and processed element-wise.  Dense batches with such a k use
 // this kernel too (k_per_row == out_offsets == nullptr).  A row longer than the ring takes
 // general_row.
-template <typename T, int NCW, int MODE>
-__global__ void __launch_bounds__(NCW * 32, 6)
-rows_ring_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t batch,
+template <typename T, int NCW, int MODE, int P = 16, int MINB = 6>
+__global__ void __launch_bounds__(NCW * 32, MINB)
+rows_ring_kernel(const char* in, char* out, int64_t batch,
                  int64_t in_pitch /*bytes*/, int rows_per_warp, int64_t D, int64_t k_dense,
-                 const int32_t* __restrict__ k_per_row, const int64_t* __restrict__ out_offsets) {
-  constexpr int PAGE = 512, P = 16, R = 8;             // 8 KiB ring per warp
+                 const int32_t* __restrict__ k_per_row, const int64_t* __restrict__ out_offsets,
+                 const int64_t* __restrict__ in_offsets) {
+  constexpr int PAGE = 512, R = 8;                     // P pages: 8 KiB ring per warp by default
   constexpr int RING = PAGE * P;
   extern __shared__ __align__(128) unsigned char ring[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(ring + (size_t)NCW * RING);
@@ -571,6 +587,11 @@ rows_ring_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t ba
   // Bytes of row `row` to stage: its prefix rounded up to 16 (the input rows are 16-byte
   // aligned and pitched, so the round-up stays inside the row), or 0 when it does not fit
   // the ring.  k_per_row == nullptr: every row keeps k_dense; out_offsets == nullptr: dense.
+  // in_offsets != nullptr: row `row` starts at element in_offsets[row] of `in` (rows gathered
+  // from several requests into one launch) instead of at row * in_pitch.
+  auto row_src = [&](int64_t row) -> const char* {
+    return in_offsets ? in + in_offsets[row] * (int64_t)sizeof(T) : in + row * in_pitch;
+  };
   auto row_plan = [&](int64_t row, char*& dst, int64_t& kr) -> uint32_t {
     kr = k_per_row ? (int64_t)k_per_row[row] : k_dense;
     if (kr > D) kr = D;
@@ -601,7 +622,7 @@ rows_ring_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t ba
         int pos = head_page, waste = 0;
         if (pos + need > P) { waste = P - pos; pos = 0; }
         if (used + waste + need > P) break;
-        bulk_load_row(smem_u32(my_ring + pos * PAGE), in + head_row * in_pitch, nb, bar0 + 8u * slot, policy);
+        bulk_load_row(smem_u32(my_ring + pos * PAGE), row_src(head_row), nb, bar0 + 8u * slot, policy);
         my_meta[slot * 3] = pos; my_meta[slot * 3 + 1] = (int)nb; my_meta[slot * 3 + 2] = waste + need;
         used += waste + need;
         head_page = pos + need == P ? 0 : pos + need;
@@ -623,7 +644,7 @@ rows_ring_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t ba
     if (row_bytes == 0) {                               // warp-uniform: odd row, nothing staged
       __syncwarp();
       if (lane == 0) { --inflight; issue_more(); }
-      general_row<T, MODE>((const T*)(in + row * in_pitch), (T*)dst, kr, lane);
+      general_row<T, MODE>((const T*)row_src(row), (T*)dst, kr, lane);
       continue;
     }
     mbar_wait(bar0 + 8u * slot, (parity >> slot) & 1u);
@@ -773,7 +794,7 @@ rows_ring_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t ba
 // A block owns rows_per_block consecutive rows.
 template <typename T, int MODE>
 __global__ void __launch_bounds__(kThreads)
-rows_wide_kernel(const char* __restrict__ in, char* __restrict__ out, int64_t batch,
+rows_wide_kernel(const char* in, char* out, int64_t batch,
                  int64_t in_pitch /*bytes*/, int nvec16, int rows_per_block) {
   extern __shared__ __align__(128) unsigned char wide[];
   __shared__ uint64_t bars[2];
@@ -919,7 +940,7 @@ template <typename T, int MODE>
 __global__ void __launch_bounds__(kThreads)
 rows_general_kernel(const T* in, T* out, int64_t batch, int64_t D,
                     int64_t k, const int32_t* __restrict__ k_per_row,
-                    const int64_t* __restrict__ out_offsets) {
+                    const int64_t* __restrict__ out_offsets, const int64_t* __restrict__ in_offsets) {
   pdl_prologue();
   const int lane = threadIdx.x & 31;
   const int64_t warp = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
@@ -927,7 +948,7 @@ rows_general_kernel(const T* in, T* out, int64_t batch, int64_t D,
   for (int64_t row = warp; row < batch; row += nwarps) {
     int64_t kr = k_per_row ? (int64_t)k_per_row[row] : k;
     if (kr > D) kr = D;
-    general_row<T, MODE>(in + row * D, out + (out_offsets ? out_offsets[row] : row * kr), kr, lane);
+    general_row<T, MODE>(in + (in_offsets ? in_offsets[row] : row * D), out + (out_offsets ? out_offsets[row] : row * kr), kr, lane);
   }
 }
 

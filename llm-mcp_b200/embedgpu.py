@@ -28,7 +28,7 @@ LIB_PATH = os.path.join(_PKG, "libembed_truncate_norm.so")
 F32, F64 = 0, 1
 TRUNCATE, TRUNCATE_RENORM = 0, 1
 ERR_NULL, ERR_SHAPE, ERR_ENUM, ERR_ALIGN, ERR_NOT_INIT, ERR_DEVICE, ERR_TOO_LARGE = -1, -2, -3, -4, -5, -6, -7
-ERR_JSON, ERR_JSON_DUP = -8, -9
+ERR_JSON, ERR_JSON_DUP, ERR_TICKET = -8, -9, -10
 STATIC_STAGE_BYTES = 16 << 20
 
 EXPORTS = (
@@ -38,6 +38,8 @@ EXPORTS = (
     "embed_truncate_norm_host_static",
     "etn_json_truncate_response", "etn_json_parse_array", "etn_json_format_array", "etn_json_prompt_tokens",
     "etn_get_counters", "etn_counter_name",
+    "embed_truncate_norm_gather", "embed_truncate_norm_ragged_host", "etn_shard_ragged", "etn_submit_host", "etn_wait",
+    "etn_note_fallback", "etn_get_histogram", "etn_histogram_name", "etn_histogram_help", "etn_raw_copy_seconds",
 )
 
 
@@ -87,6 +89,19 @@ def lib() -> ctypes.CDLL:
         L.etn_get_counters.argtypes = [vp, ci]
         L.etn_counter_name.argtypes = [ci]
         L.etn_counter_name.restype = ctypes.c_char_p
+        L.embed_truncate_norm_gather.argtypes = [i64, vp, vp, vp, ci, ci, vp, vp, vp]
+        L.embed_truncate_norm_ragged_host.argtypes = [i64, i64, vp, ci, ci, vp, i64, vp, ci]
+        L.etn_shard_ragged.argtypes = [i64, i64, vp, ci, vp]
+        L.etn_submit_host.argtypes = [i64, i64, i64, vp, ci, ci, vp, i64, vp, ci, ctypes.POINTER(i64)]
+        L.etn_wait.argtypes = [i64]
+        L.etn_note_fallback.argtypes = [i64]
+        L.etn_note_fallback.restype = None
+        L.etn_get_histogram.argtypes = [ci, vp, vp, ci, vp]
+        L.etn_histogram_name.argtypes = [ci]
+        L.etn_histogram_name.restype = ctypes.c_char_p
+        L.etn_histogram_help.argtypes = [ci]
+        L.etn_histogram_help.restype = ctypes.c_char_p
+        L.etn_raw_copy_seconds.argtypes = [vp, vp, ctypes.c_size_t, ci, ci, vp]
         _lib = L
     return _lib
 
@@ -174,6 +189,48 @@ def truncate_norm_host(x: np.ndarray, k: int, mode: int = TRUNCATE_RENORM, out: 
     return out
 
 
+def truncate_norm_ragged_host(x: np.ndarray, k_per_row, mode: int = TRUNCATE_RENORM, out: np.ndarray | None = None,
+                              n_devices: int = 0) -> np.ndarray:
+    """embed_truncate_norm_ragged_host: row r keeps min(k_per_row[r], D) components; the result is
+    the rows packed back to back (1-D).  One call for responses of requests that resolved
+    different `dimensions` (handlers.go:1874-1877)."""
+    if x.ndim != 2 or x.strides[1] != x.itemsize:
+        raise ValueError("x must be 2-D with unit column stride")
+    batch, D = x.shape
+    kpr = np.ascontiguousarray(k_per_row, dtype=np.int32)
+    if kpr.shape != (batch,):
+        raise ValueError("k_per_row must have one entry per row")
+    total = int(np.clip(kpr.astype(np.int64), 0, D).sum())
+    if out is None:
+        out = np.empty(total, dtype=x.dtype)
+    pitch = x.strides[0] if batch > 1 else D * x.itemsize
+    check(lib().embed_truncate_norm_ragged_host(batch, D, kpr.ctypes.data if batch else None, dtype_code(x.dtype), mode,
+                                                x.ctypes.data if batch else None, pitch,
+                                                out.ctypes.data if total else (x.ctypes.data if batch else None), n_devices),
+          "embed_truncate_norm_ragged_host")
+    return out
+
+
+class Ticket:
+    """etn_submit_host / etn_wait: a host call in flight.  Keeps its buffers alive until waited for."""
+
+    def __init__(self, x: np.ndarray, k: int, mode: int = TRUNCATE_RENORM, out: np.ndarray | None = None, n_devices: int = 0):
+        if x.ndim != 2 or x.strides[1] != x.itemsize:
+            raise ValueError("x must be 2-D with unit column stride")
+        batch, D = x.shape
+        self.x = x
+        self.out = np.empty((batch, min(int(k), D)), dtype=x.dtype) if out is None else out
+        t = ctypes.c_int64(0)
+        pitch = x.strides[0] if batch > 1 else D * x.itemsize
+        check(lib().etn_submit_host(batch, D, k, None, dtype_code(x.dtype), mode, x.ctypes.data if batch else None, pitch,
+                                    self.out.ctypes.data if batch else None, n_devices, ctypes.byref(t)), "etn_submit_host")
+        self.ticket = t.value
+
+    def wait(self) -> np.ndarray:
+        check(lib().etn_wait(self.ticket), "etn_wait")
+        return self.out
+
+
 # --------------------------------------------------------- reference call-site mirror ----
 def getenv_int(key: str, default: int, env=None) -> int:
     """config.GetenvInt (config.go:17-24): unset, empty or not an integer -> default."""
@@ -214,6 +271,9 @@ def truncate_embeddings(result: Any, dims: int, renorm: bool | None = None) -> d
     prefix is L2-renormalised as well.  Vectors are packed per source length into pinned
     buffers and each group goes through one ``embed_truncate_norm_host`` call; a vector
     holding anything but JSON numbers cannot be packed and gets the reference reslice.
+    Without ``renorm`` nothing is computed, so — exactly like the Go binding
+    (go/embedgpu/embedgpu.go) — every vector gets the reference's O(1) reslice and the GPU is
+    not involved (no PCIe round trip to take a slice; integer elements stay integers).
     Returns counters {"gpu_vectors", "resliced_vectors", "launch_groups"}.
     """
     stats = {"gpu_vectors": 0, "resliced_vectors": 0, "launch_groups": 0}
@@ -231,12 +291,14 @@ def truncate_embeddings(result: Any, dims: int, renorm: bool | None = None) -> d
         emb = item.get("embedding")
         if not isinstance(emb, list) or len(emb) <= dims:
             continue
-        if _packable(emb):
+        if renorm and _packable(emb):
             groups.setdefault(len(emb), []).append(item)
         else:
             item["embedding"] = emb[:dims]
             stats["resliced_vectors"] += 1
-    mode = TRUNCATE_RENORM if renorm else TRUNCATE
+    if renorm and stats["resliced_vectors"]:
+        lib().etn_note_fallback(stats["resliced_vectors"])      # renorm was asked for and could not be done
+    mode = TRUNCATE_RENORM
     for D, items in groups.items():
         n = len(items)
         pin_in, pin_out = PinnedBuffer(n * D * 8), PinnedBuffer(n * dims * 8)
@@ -268,19 +330,14 @@ def shard_rows(batch: int, world: int) -> list[tuple[int, int]]:
 
 def shard_ragged(k_per_row, D: int, world: int) -> list[tuple[int, int]]:
     """Contiguous row ranges of a ragged batch balanced by bytes moved (sum of min(k, D)),
-    not by row count: the cost of a row is proportional to its k."""
-    kk = np.minimum(np.asarray(k_per_row, dtype=np.int64), D)
+    not by row count: the cost of a row is proportional to its k.  The cut
+    points are etn_shard_ragged's, the ones embed_truncate_norm_ragged_host uses itself:
+    shard g starts at the first row r with (kept elements before r) * world >= total * g."""
     if world < 1:
         raise ValueError("world >= 1")
-    n = len(kk)
-    csum = np.concatenate([[0], np.cumsum(kk)])
-    total = int(csum[-1])
-    cuts = [0]
-    for g in range(1, world):
-        target = total * g / world
-        cuts.append(int(np.searchsorted(csum, target, side="left")))
-    cuts.append(n)
-    cuts = np.maximum.accumulate(np.minimum(cuts, n))
+    kpr = np.ascontiguousarray(k_per_row, dtype=np.int32)
+    cuts = np.zeros(world + 1, dtype=np.int64)
+    check(lib().etn_shard_ragged(len(kpr), D, kpr.ctypes.data if len(kpr) else None, world, cuts.ctypes.data), "etn_shard_ragged")
     return [(int(cuts[g]), int(cuts[g + 1])) for g in range(world)]
 
 
@@ -324,9 +381,41 @@ def counters() -> dict[str, int]:
     return {lib().etn_counter_name(i).decode(): int(buf[i]) for i in range(n)}
 
 
+HIST_BATCH_ROWS, HIST_KERNEL_SECONDS, HIST_H2D_SECONDS, HIST_D2H_SECONDS, HIST_CALL_SECONDS, HIST_REQS_PER_LAUNCH = range(6)
+HIST_COUNT = 6
+
+
+def histogram(which: int) -> dict:
+    """etn_get_histogram as {"name", "help", "le": [...], "counts": [...per bucket...], "sum", "count"}."""
+    L = lib()
+    n = L.etn_get_histogram(which, None, None, 0, None)
+    if n < 0:
+        raise EtnError(n, strerror(n), "etn_get_histogram")
+    le, cnt, total = (ctypes.c_double * n)(), (ctypes.c_int64 * n)(), ctypes.c_double(0)
+    check(min(0, L.etn_get_histogram(which, le, cnt, n, ctypes.byref(total))), "etn_get_histogram")
+    counts = [int(c) for c in cnt]
+    return {"name": L.etn_histogram_name(which).decode(), "help": L.etn_histogram_help(which).decode(),
+            "le": [float(v) for v in le], "counts": counts, "sum": float(total.value), "count": sum(counts)}
+
+
+def _fmt_le(v: float) -> str:
+    return "+Inf" if v == float("inf") else repr(float(v)) if v != int(v) else str(int(v))
+
+
 def metrics_text() -> str:
-    """Prometheus text exposition of the counters (the /metrics route, server.go:61)."""
-    return "".join(f"# TYPE {k} counter\n{k} {v}\n" for k, v in counters().items())
+    """Prometheus text exposition of the counters and histograms (the /metrics route,
+    server.go:61): what promauto.NewCounter / NewHistogram collectors registered beside
+    metrics.go:9-26 would write — cumulative `le` buckets, `_sum`, `_count`."""
+    out = [f"# TYPE {k} counter\n{k} {v}\n" for k, v in counters().items()]
+    for w in range(HIST_COUNT):
+        h = histogram(w)
+        out.append(f"# HELP {h['name']} {h['help']}\n# TYPE {h['name']} histogram\n")
+        run = 0
+        for le, c in zip(h["le"], h["counts"]):
+            run += c
+            out.append(f'{h["name"]}_bucket{{le="{_fmt_le(le)}"}} {run}\n')
+        out.append(f"{h['name']}_sum {h['sum']!r}\n{h['name']}_count {h['count']}\n")
+    return "".join(out)
 
 
 # ------------------------------------------------------------ typed vectors (N2) ----
@@ -342,13 +431,15 @@ def truncate_typed(embeddings, dims: int, renorm: bool | None = None) -> list:
     out = [list(v) if not isinstance(v, list) else v for v in embeddings]
     if dims <= 0:
         return out
+    if not renorm:                                   # a slice needs no GPU (as in the Go TruncateTyped)
+        return [v[:dims] if len(v) > dims else v for v in out]
     groups: dict[int, list[int]] = {}
     for i, v in enumerate(out):
         if len(v) > dims:
             groups.setdefault(len(v), []).append(i)
     for D, idx in groups.items():
         x = np.array([out[i] for i in idx], dtype=np.float64)
-        y = truncate_norm_host(x, dims, TRUNCATE_RENORM if renorm else TRUNCATE)
+        y = truncate_norm_host(x, dims, TRUNCATE_RENORM)
         for r, i in enumerate(idx):
             out[i] = y[r].tolist()
     return out
@@ -373,14 +464,16 @@ def truncate_job_results(results: list, dims: int, renorm: bool | None = None) -
         emb = data.get("embedding") if isinstance(data, dict) else None
         if not isinstance(emb, list) or len(emb) <= dims:
             continue
-        if _packable(emb):
+        if renorm and _packable(emb):
             groups.setdefault(len(emb), []).append(data)
         else:
             data["embedding"] = emb[:dims]
             stats["resliced_vectors"] += 1
+    if renorm and stats["resliced_vectors"]:
+        lib().etn_note_fallback(stats["resliced_vectors"])
     for D, items in groups.items():
         x = np.array([it["embedding"] for it in items], dtype=np.float64)
-        y = truncate_norm_host(x, dims, TRUNCATE_RENORM if renorm else TRUNCATE)
+        y = truncate_norm_host(x, dims, TRUNCATE_RENORM)
         for r, it in enumerate(items):
             it["embedding"] = y[r].tolist()
         stats["gpu_vectors"] += len(items)

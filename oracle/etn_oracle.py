@@ -157,6 +157,27 @@ def ragged(x: np.ndarray, k_per_row: np.ndarray, mode: int) -> tuple[np.ndarray,
     return out, off
 
 
+def shard_ragged_ref(k_per_row, D: int, world: int) -> list[tuple[int, int]]:
+    """Contiguous row ranges of a ragged batch balanced by kept elements:
+    shard g starts at the first row r with (kept elements before r) * world >= total * g.
+    Plain Python integers; the checker for etn_shard_ragged and for the cuts
+    embed_truncate_norm_ragged_host makes.  Each vector is independent in the reference
+    (handlers.go:2068-2076), so any contiguous cut is legal; this one is the balanced one."""
+    kept = [min(max(int(k), 0), D) for k in k_per_row]
+    csum = [0]
+    for v in kept:
+        csum.append(csum[-1] + v)
+    n, total = len(kept), csum[-1]
+    cuts = [0]
+    for g in range(1, world):
+        r = cuts[-1]
+        while r < n and csum[r] * world < total * g:
+            r += 1
+        cuts.append(r)
+    cuts.append(n)
+    return [(cuts[g], cuts[g + 1]) for g in range(world)]
+
+
 def max_ulp(a: np.ndarray, b: np.ndarray) -> tuple[int, int]:
     """(largest ulp distance, flat index); distance -1 means a NaN was seen."""
     a = np.ascontiguousarray(a)

@@ -37,7 +37,7 @@ def test_header_cites_the_reference_per_entry_point():
 
 def test_version_and_strerror():
     L = eg.lib()
-    assert L.etn_version() == 100
+    assert L.etn_version() == 200
     assert eg.strerror(0) == "ok"
     for code in (eg.ERR_NULL, eg.ERR_SHAPE, eg.ERR_ENUM, eg.ERR_ALIGN, eg.ERR_NOT_INIT, eg.ERR_DEVICE):
         assert eg.strerror(code) not in ("ok", "unknown error")
@@ -90,7 +90,8 @@ def test_host_mirror_config_surface():
 
 def test_counters_and_typed_mirror_need_no_device():
     c0 = eg.counters()
-    assert list(c0) == [eg.lib().etn_counter_name(i).decode() for i in range(8)] and all(k.startswith("llmcore_embed_gpu_") for k in c0)
+    assert list(c0) == [eg.lib().etn_counter_name(i).decode() for i in range(10)] and all(k.startswith("llmcore_embed_gpu_") for k in c0)
+    assert "llmcore_embed_gpu_fallback_total" in c0 and "llmcore_embed_gpu_errors_total" in c0
     eg.lib().embed_truncate_norm(2, 8, 0, eg.F64, None, None, None)          # shape error: counted nowhere but...
     p = (ctypes.c_double * 4)()
     assert eg.lib().embed_truncate_norm_host(2, 8, 4, eg.F64, 1, ctypes.addressof(p), 0, ctypes.addressof(p), 0) == eg.ERR_NOT_INIT
@@ -98,3 +99,56 @@ def test_counters_and_typed_mirror_need_no_device():
     # N2 mirror: nothing to cut -> no device needed, input returned as is
     assert eg.truncate_typed([[1.0, 2.0], [3.0]], 2) == [[1.0, 2.0], [3.0]]
     assert eg.truncate_typed([[1.0, 2.0, 3.0]], 0) == [[1.0, 2.0, 3.0]]
+
+
+def test_new_host_entry_points_reject_bad_arguments_without_a_device():
+    L = eg.lib()
+    buf = (ctypes.c_double * 16)()
+    kpr = (ctypes.c_int32 * 2)(4, 4)
+    p, pk = ctypes.addressof(buf), ctypes.addressof(kpr)
+    assert L.embed_truncate_norm_ragged_host(0, 8, None, eg.F64, 1, None, 0, None, 0) == 0
+    assert L.embed_truncate_norm_ragged_host(2, 8, None, eg.F64, 1, p, 0, p, 0) == eg.ERR_NULL
+    assert L.embed_truncate_norm_ragged_host(2, 8, pk, 7, 1, p, 0, p, 0) == eg.ERR_ENUM
+    assert L.embed_truncate_norm_ragged_host(2, 0, pk, eg.F64, 1, p, 0, p, 0) == eg.ERR_SHAPE
+    assert L.embed_truncate_norm_ragged_host(2, 8, pk, eg.F64, 1, p, 4, p, 0) == eg.ERR_SHAPE
+    assert L.embed_truncate_norm_ragged_host(2, 8, pk, eg.F64, 1, p, 0, p, 0) == eg.ERR_NOT_INIT
+    t = ctypes.c_int64(0)
+    assert L.etn_submit_host(2, 8, 4, None, eg.F64, 1, p, 0, p, 0, None) == eg.ERR_NULL
+    assert L.etn_submit_host(2, 8, 4, None, eg.F64, 1, p, 0, p, 0, ctypes.byref(t)) == eg.ERR_NOT_INIT and t.value == 0
+    assert L.etn_submit_host(0, 8, 4, None, eg.F64, 1, None, 0, None, 0, ctypes.byref(t)) == 0 and t.value > 0
+    assert L.etn_wait(t.value) == 0                      # empty batch: nothing to wait for
+    assert L.etn_wait(t.value) == eg.ERR_TICKET and L.etn_wait(123456789) == eg.ERR_TICKET
+    assert "ticket" in eg.strerror(eg.ERR_TICKET)
+    assert L.embed_truncate_norm_gather(2, None, pk, p, eg.F64, 1, p, p, None) == eg.ERR_NULL
+    assert L.embed_truncate_norm_gather(0, None, None, None, eg.F64, 1, None, None, None) == 0
+    assert L.embed_truncate_norm(2, 8, 4, eg.F64, p, p, None) == eg.ERR_SHAPE      # in place needs k >= D
+    assert L.etn_shard_ragged(2, 8, pk, 0, p) == eg.ERR_SHAPE and L.etn_shard_ragged(2, 8, None, 2, p) == eg.ERR_NULL
+
+
+def test_histograms_and_prometheus_exposition():
+    """N3: fixed-bucket histograms beside metrics.go:18-26, exported as cumulative `le` series."""
+    import math
+    names = []
+    for w in range(eg.HIST_COUNT):
+        h = eg.histogram(w)
+        names.append(h["name"])
+        assert h["name"].startswith("llmcore_embed_gpu_") and h["help"]
+        assert h["le"][-1] == math.inf and h["le"] == sorted(h["le"]) and len(h["le"]) == len(h["counts"])
+    assert names == ["llmcore_embed_gpu_batch_rows", "llmcore_embed_gpu_kernel_seconds", "llmcore_embed_gpu_h2d_seconds",
+                     "llmcore_embed_gpu_d2h_seconds", "llmcore_embed_gpu_call_seconds", "llmcore_embed_gpu_requests_per_launch"]
+    assert eg.lib().etn_get_histogram(99, None, None, 0, None) == eg.ERR_ENUM
+    le = (ctypes.c_double * 2)()
+    cnt = (ctypes.c_int64 * 2)()
+    assert eg.lib().etn_get_histogram(0, le, cnt, 2, None) == eg.ERR_SHAPE
+    text = eg.metrics_text()
+    for n in names:
+        assert f"# TYPE {n} histogram" in text and f'{n}_bucket{{le="+Inf"}}' in text
+        assert f"{n}_sum " in text and f"{n}_count " in text
+    # cumulative buckets never decrease and the +Inf bucket equals _count
+    import re
+    for n in names:
+        vals = [int(v) for v in re.findall(rf"^{n}_bucket{{[^}}]*}} (\d+)$", text, re.M)]
+        assert vals == sorted(vals) and vals[-1] == int(re.search(rf"^{n}_count (\d+)$", text, re.M).group(1))
+    before = eg.counters()["llmcore_embed_gpu_fallback_total"]
+    eg.lib().etn_note_fallback(3)
+    assert eg.counters()["llmcore_embed_gpu_fallback_total"] == before + 3

@@ -37,6 +37,17 @@ def test_shard_ragged_balances_bytes_not_rows():
     assert eg.shard_ragged(np.array([5000, 5000]), 100, 2) == [(0, 1), (1, 2)]   # k clamps to D
 
 
+def test_shard_ragged_equals_the_oracle_cut(oracle):
+    """etn_shard_ragged (C++, the cut embed_truncate_norm_ragged_host makes itself) against the
+    plain-Python restatement, on random and on degenerate length patterns."""
+    rng = np.random.default_rng(11)
+    cases = [rng.integers(1, 1500, size=n) for n in (0, 1, 2, 7, 100, 5000)]
+    cases += [np.ones(50, dtype=np.int64), np.full(64, 1024), np.array([1, 1, 900, 1, 1, 900, 1]), np.array([10 ** 6] * 5)]
+    for kpr in cases:
+        for world in (1, 2, 3, 8):
+            assert eg.shard_ragged(kpr, 1024, world) == oracle.shard_ragged_ref(kpr, 1024, world), (kpr[:8], world)
+
+
 def _free_port():
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
@@ -57,12 +68,21 @@ def _rank_main(rank, world, port, q):
         elapsed = torch.tensor([0.010 * (rank + 1)], dtype=torch.float64)
         dist.barrier()
         dist.all_reduce(elapsed, op=dist.ReduceOp.MAX)             # bench.py's max over ranks
+        # C5-style: a ragged batch cut by kept bytes, every rank renormalises its own range
+        rng = np.random.default_rng(5)
+        kpr = rng.choice([64, 128, 256, 512], size=batch).astype(np.int32)
+        rlo, rhi = eg.shard_ragged(kpr, D, world)[rank]
+        xr = oracle.fill(5, rhi - rlo, D, np.float64, row0=rlo)
+        yr, _ = oracle.ragged(xr, kpr[rlo:rhi], 1)
         gathered = [None] * world
-        dist.all_gather_object(gathered, (lo, hi, y))              # test-only gather
+        dist.all_gather_object(gathered, (lo, hi, y, rlo, rhi, yr))  # test-only gather
         if rank == 0:
             full = np.concatenate([g[2] for g in sorted(gathered, key=lambda g: g[0])])
             want = oracle.renorm_exact(oracle.fill(2, batch, D, np.float32), k)
-            q.put((bool(np.array_equal(full, want)), float(elapsed.item()), [g[:2] for g in gathered]))
+            rag = np.concatenate([g[5] for g in sorted(gathered, key=lambda g: g[3])])
+            rag_want, _ = oracle.ragged(oracle.fill(5, batch, D, np.float64), kpr, 1)
+            same = bool(np.array_equal(full, want)) and bool(np.array_equal(rag, rag_want))
+            q.put((same, float(elapsed.item()), [g[:2] for g in gathered]))
     finally:
         dist.destroy_process_group()
 

@@ -85,3 +85,51 @@ def test_static_entry_point_limits_and_errors():
     rc, out = _static(xs, 4, eg.TRUNCATE_RENORM, ctypes.c_void_p(s.cuda_stream))
     assert rc == 0
     assert np.allclose(out, xs[:, :4] / np.linalg.norm(xs[:, :4], axis=1, keepdims=True), rtol=1e-15)
+
+
+def test_static_entry_point_concurrent_callers_and_no_allocation(oracle):
+    """Callers on different threads and streams share the one built-in array: the library
+    queues them behind a per-device lock, so each gets its own rows back.  And the point of
+    the entry point — free device memory is the same before and after a call (the first call
+    on the device, which loads the kernels, is made beforehand)."""
+    import threading
+    torch.cuda.set_device(0)
+    xs = [oracle.fill(70 + t, 1500 + 100 * t, 1024, np.float32) for t in range(4)]
+    wants = [oracle.renorm_exact(x, 256) for x in xs]
+    rc, _ = _static(xs[0], 256, eg.TRUNCATE_RENORM)
+    assert rc == 0
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    errs = []
+
+    def caller(t):
+        try:
+            torch.cuda.set_device(0)
+            s = torch.cuda.Stream()
+            for _ in range(8):
+                rc, got = _static(xs[t], 256, eg.TRUNCATE_RENORM, ctypes.c_void_p(s.cuda_stream))
+                assert rc == 0, eg.strerror(rc)
+                d, _ = oracle.max_ulp(got, wants[t])
+                assert 0 <= d <= 2, d
+        except Exception as e:  # noqa: BLE001
+            errs.append((t, repr(e)))
+
+    before = eg.counters()
+    th = [threading.Thread(target=caller, args=(t,)) for t in range(4)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not errs, errs
+    after = eg.counters()
+    assert after["llmcore_embed_gpu_host_calls_total"] - before["llmcore_embed_gpu_host_calls_total"] == 32
+    assert after["llmcore_embed_gpu_host_rows_total"] - before["llmcore_embed_gpu_host_rows_total"] == 8 * sum(len(x) for x in xs)
+    # one more plain call with nothing else running: free memory unchanged
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info()
+    rc, _ = _static(xs[1], 256, eg.TRUNCATE_RENORM)
+    free2, _ = torch.cuda.mem_get_info()
+    assert rc == 0 and free2 == free1, (free0, free1, free2)
+    # a refused size is counted as "take the other path", not as an error
+    f0, e0 = eg.counters()["llmcore_embed_gpu_fallback_total"], eg.counters()["llmcore_embed_gpu_errors_total"]
+    big = np.zeros((eg.STATIC_STAGE_BYTES // 4096 + 1, 1024), dtype=np.float32)
+    assert _static(big, 1024, eg.TRUNCATE_RENORM)[0] == eg.ERR_TOO_LARGE
+    assert eg.counters()["llmcore_embed_gpu_fallback_total"] == f0 + 1 and eg.counters()["llmcore_embed_gpu_errors_total"] == e0

@@ -311,6 +311,61 @@ static void pcie_study(Timer& tm) {
   CK(cudaFreeHost(hin)); CK(cudaFreeHost(hout)); CK(cudaFree(din)); CK(cudaFree(dout));
 }
 
+// Page-ring kernel (ragged / gathered rows): ring pages per warp x resident blocks, on the
+// config-5 length mix and on 64 merged C1 requests (uniform 8 KiB float64 rows).
+template <int P, int MINB>
+void ring_variant(const char* label, const char* in, char* out, int64_t rows, int64_t D, const int32_t* d_k,
+                  const int64_t* d_off, double algo_bytes, Timer& tm) {
+  constexpr int NCW = 4;
+  auto kern = rows_ring_kernel<double, NCW, kModeRenorm, P, MINB>;
+  const size_t smem = (size_t)NCW * P * 512 + (size_t)NCW * 8 * 8 + (size_t)NCW * 8 * 3 * 4;
+  CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 0;
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, NCW * 32, smem));
+  for (int rpw : {4, 8, 16, 32}) {
+    const int64_t blocks = (rows + (int64_t)NCW * rpw - 1) / ((int64_t)NCW * rpw);
+    double ms = tm.ms([&](int) {
+      kern<<<(unsigned)blocks, NCW * 32, smem>>>(in, out, rows, D * 8, rpw, D, 0, d_k, d_off, nullptr);
+    }, 3, g_iters);
+    CK(cudaGetLastError());
+    printf("%-28s ring P=%2d (%2d KiB/warp) minb=%d occ=%d rpw=%2d %8.3f ms %8.1f GB/s\n", label, P, P / 2, MINB, per_sm, rpw, ms,
+           algo_bytes / ms / 1e6);
+  }
+}
+
+void ring_study(Timer& tm) {
+  const int64_t D = 4096;
+  for (int which = 0; which < 2; ++which) {
+    const int64_t rows = which == 0 ? 1048576 : 65536;
+    std::vector<int32_t> k(rows);
+    std::vector<int64_t> off(rows);
+    uint64_t st = 5;
+    auto rnd = [&] { st = st * 6364136223846793005ull + 1442695040888963407ull; return (uint32_t)(st >> 33); };
+    const int ks[5] = {64, 128, 256, 512, 1024};
+    int64_t r = 0, acc = 0;
+    while (r < rows) {
+      int64_t m = which == 0 ? 1 + rnd() % 2048 : rows;
+      const int kk = which == 0 ? ks[rnd() % 5] : 1024;
+      for (; m > 0 && r < rows; --m, ++r) { k[r] = kk; off[r] = acc; acc += kk; }
+    }
+    char *in, *out; int32_t* d_k; int64_t* d_off;
+    CK(cudaMalloc(&in, rows * D * 8)); CK(cudaMalloc(&out, acc * 8));
+    CK(cudaMalloc(&d_k, rows * 4)); CK(cudaMalloc(&d_off, rows * 8));
+    fill_kernel<double><<<148 * 16, 256>>>((double*)in, 5, 0, rows, D, D, D);
+    CK(cudaMemcpy(d_k, k.data(), rows * 4, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(d_off, off.data(), rows * 8, cudaMemcpyHostToDevice));
+    CK(cudaDeviceSynchronize());
+    const char* label = which == 0 ? "C5 mix 1Mi rows" : "64 x C1 (8 KiB rows)";
+    const double algo = 16.0 * acc;
+    ring_variant<16, 6>(label, in, out, rows, D, d_k, d_off, algo, tm);
+    ring_variant<16, 4>(label, in, out, rows, D, d_k, d_off, algo, tm);
+    ring_variant<32, 3>(label, in, out, rows, D, d_k, d_off, algo, tm);
+    ring_variant<24, 4>(label, in, out, rows, D, d_k, d_off, algo, tm);
+    ring_variant<48, 2>(label, in, out, rows, D, d_k, d_off, algo, tm);
+    CK(cudaFree(in)); CK(cudaFree(out)); CK(cudaFree(d_k)); CK(cudaFree(d_off));
+  }
+}
+
 int main(int argc, char** argv) {
   if (argc > 1) g_filter = argv[1];
   if (getenv("ITERS")) g_iters = atoi(getenv("ITERS"));
@@ -320,6 +375,7 @@ int main(int argc, char** argv) {
   Timer tm;
   if (g_filter && !strcmp(g_filter, "pcie")) { pcie_study(tm); return 0; }
   if (g_filter && !strcmp(g_filter, "c1")) { c1_study(tm); return 0; }
+  if (g_filter && !strcmp(g_filter, "ring")) { ring_study(tm); return 0; }
   if (g_filter && !strcmp(g_filter, "small")) {
     for (bool pdl : {false, true}) {
       run_reg_small<float, 32, 1, 4, 1, 4, 32>("C2 64Kx768->256", 65536, 768, 256, 4, tm, pdl);
