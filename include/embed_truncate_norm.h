@@ -124,7 +124,12 @@ ETN_API int embed_truncate_norm_gather(int64_t batch, const int64_t *in_offsets,
  *                                others to share its launch (default 0: only requests that
  *                                are already queued are merged)
  *   EMBED_GPU_MIN_DEVICE_BYTES   kept-prefix bytes a device must get before a call is split
- *                                over one more device (default 4 MiB) */
+ *                                over one more device (default 4 MiB)
+ *   EMBED_GPU_TIMING             every n-th staged chunk is timed with CUDA events for the
+ *                                histograms (default 16; 1 = every chunk, 0 = none: the four
+ *                                timestamped records cost a small request a quarter of its time)
+ *   EMBED_GPU_PIECES             chunks a lone request is cut into so that its D2H overlaps
+ *                                its own H2D (default 4) */
 ETN_API int etn_init(const int *device_ids, int n_devices);
 
 /* Releases what etn_init created (main.go:118-122, graceful shutdown). */
@@ -298,8 +303,9 @@ ETN_API void etn_note_fallback(int64_t vectors);
  * (the last one is +Inf) and counts[i] = samples in bucket i (NOT cumulative; Prometheus'
  * `le` series is the running sum) and returns the number of buckets; *sum receives the sum of
  * all samples.  With both arrays NULL it only returns the number of buckets.  Kernel and
- * copy times come from CUDA events the host path records around every staged chunk and reads
- * when the chunk retires, so nothing synchronises for the sake of a metric. */
+ * copy times come from CUDA events the host path records around every n-th staged chunk
+ * (EMBED_GPU_TIMING, default 16: a sample, not a census) and reads when the chunk retires, so
+ * nothing synchronises for the sake of a metric. */
 #define ETN_HIST_BATCH_ROWS 0      /* rows per host-path call */
 #define ETN_HIST_KERNEL_SECONDS 1  /* kernel time per staged chunk */
 #define ETN_HIST_H2D_SECONDS 2     /* host-to-device copy time per staged chunk */

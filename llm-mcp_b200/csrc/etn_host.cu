@@ -124,10 +124,12 @@ struct Slot {
 
 // One staged chunk in flight.  Chunks retire in the order they were issued.
 struct Chunk {
-  cudaEvent_t ev[4] = {};          // before H2D, after H2D, after the kernel, after D2H
+  cudaEvent_t ev[4] = {};          // before H2D, after H2D, after the kernel, after D2H (timed chunks only)
+  cudaEvent_t done = nullptr;      // after D2H, every chunk; no timestamp, so recording it is cheap
   int slot = 0;
   std::vector<Job*> jobs;          // jobs with a piece in this chunk
   bool has_kernel = false;
+  bool timed = true;               // ev[0..3] recorded (kernel and copy times for the histograms)
   bool failed = false;             // issuing stopped half way: the stream was drained on the spot
 };
 constexpr int kChunkRecs = 16;     // chunks in flight per device (four deep on each slot's stream)
@@ -150,6 +152,11 @@ struct Runtime {
   std::vector<std::unique_ptr<Device>> devs;
   int64_t max_wait_us = 0;
   int64_t min_device_bytes = 4 << 20;
+  // Measured (profiles/r02_latency.txt): the four timestamped event records cost a 64-row request
+  // 20 of its 73 us and a C1 request 50 of 384 us, and four pieces beat eight once every piece
+  // carries its own completion event.  Hence: every 16th chunk is timed, four pieces.
+  int64_t timing_every = 16;       // EMBED_GPU_TIMING: time every n-th staged chunk (1 = all, 0 = none)
+  int64_t pieces = kSlots;         // EMBED_GPU_PIECES: chunks a lone job is cut into
   std::atomic<uint32_t> rr{0};
   ~Runtime();
 };
@@ -188,22 +195,21 @@ void retire_oldest(Device* d) {
   Chunk& c = d->rec[d->retired % kChunkRecs];
   cudaError_t e = cudaSuccess;
   if (!c.failed) {
-    e = cudaEventSynchronize(c.ev[3]);
-    if (e == cudaSuccess) {
-      float ms = 0.f;
-      if (cudaEventElapsedTime(&ms, c.ev[0], c.ev[1]) == cudaSuccess) observe(ETN_HIST_H2D_SECONDS, ms * 1e-3);
-      if (c.has_kernel && cudaEventElapsedTime(&ms, c.ev[1], c.ev[2]) == cudaSuccess)
-        observe(ETN_HIST_KERNEL_SECONDS, ms * 1e-3);
-      if (cudaEventElapsedTime(&ms, c.ev[2], c.ev[3]) == cudaSuccess) observe(ETN_HIST_D2H_SECONDS, ms * 1e-3);
-    } else {
-      cudaGetLastError();
-    }
+    e = cudaEventSynchronize(c.done);
+    if (e != cudaSuccess) cudaGetLastError();
   }
-  for (Job* j : c.jobs) {
+  for (Job* j : c.jobs) {                              // callers first, bookkeeping after
     if (e != cudaSuccess && !j->rc) j->rc = (int)e;
     if (--j->pending == 0 && j->issued_all) complete(d, j);
   }
   c.jobs.clear();
+  if (!c.failed && c.timed && e == cudaSuccess) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, c.ev[0], c.ev[1]) == cudaSuccess) observe(ETN_HIST_H2D_SECONDS, ms * 1e-3);
+    if (c.has_kernel && cudaEventElapsedTime(&ms, c.ev[1], c.ev[2]) == cudaSuccess)
+      observe(ETN_HIST_KERNEL_SECONDS, ms * 1e-3);
+    if (cudaEventElapsedTime(&ms, c.ev[2], c.ev[3]) == cudaSuccess) observe(ETN_HIST_D2H_SECONDS, ms * 1e-3);
+  }
   ++d->retired;
 }
 
@@ -241,7 +247,7 @@ int issue_dense(Device* d, Slot& s, Chunk& ck, const std::vector<Seg>& segs) {
   int64_t* m_out = m_in + kMaxMetaRows;
   int32_t* m_k = reinterpret_cast<int32_t*>(m_out + kMaxMetaRows);
   if (!uniform) { wait_for_meta(d, s); s.meta_seq = d->issued; }
-  ETN_TRY(cudaEventRecord(ck.ev[0], s.stream));
+  if (ck.timed) ETN_TRY(cudaEventRecord(ck.ev[0], s.stream));
   std::vector<int64_t> out_off(segs.size());
   int64_t in_b = 0, out_b = 0, row = 0;
   for (size_t i = 0; i < segs.size(); ++i) {
@@ -266,9 +272,9 @@ int issue_dense(Device* d, Slot& s, Chunk& ck, const std::vector<Seg>& segs) {
   bool from_in = false;                               // TRUNCATE of one-k segments: copy back what came in
   if (uniform && c0->mode == ETN_TRUNCATE) {
     from_in = true;
-    ETN_TRY(cudaEventRecord(ck.ev[1], s.stream));
+    if (ck.timed) ETN_TRY(cudaEventRecord(ck.ev[1], s.stream));
   } else if (uniform) {
-    ETN_TRY(cudaEventRecord(ck.ev[1], s.stream));
+    if (ck.timed) ETN_TRY(cudaEventRecord(ck.ev[1], s.stream));
     if (int rc = etn_rt::run_dense(total, ip0 / es, c0->kk, c0->dtype, c0->mode, s.d_in, s.d_out, s.stream)) return rc;
     ck.has_kernel = true;
   } else {
@@ -278,13 +284,13 @@ int issue_dense(Device* d, Slot& s, Chunk& ck, const std::vector<Seg>& segs) {
     ETN_TRY(cudaMemcpyAsync(d_in_off, m_in, (size_t)total * 8, cudaMemcpyHostToDevice, s.stream));
     ETN_TRY(cudaMemcpyAsync(d_out_off, m_out, (size_t)total * 8, cudaMemcpyHostToDevice, s.stream));
     ETN_TRY(cudaMemcpyAsync(d_k, m_k, (size_t)total * 4, cudaMemcpyHostToDevice, s.stream));
-    ETN_TRY(cudaEventRecord(ck.ev[1], s.stream));
+    if (ck.timed) ETN_TRY(cudaEventRecord(ck.ev[1], s.stream));
     if (int rc = etn_rt::run_rows(total, INT64_MAX / 16, d_k, d_out_off, d_in_off, c0->dtype, c0->mode, s.d_in,
                                   s.d_out, s.stream))
       return rc;
     ck.has_kernel = true;
   }
-  ETN_TRY(cudaEventRecord(ck.ev[2], s.stream));
+  if (ck.timed) ETN_TRY(cudaEventRecord(ck.ev[2], s.stream));
   int64_t in_seg = 0;
   for (size_t i = 0; i < segs.size(); ++i) {
     const Seg& g = segs[i];
@@ -300,7 +306,8 @@ int issue_dense(Device* d, Slot& s, Chunk& ck, const std::vector<Seg>& segs) {
                                 cudaMemcpyDeviceToHost, s.stream));
     in_seg += g.n * ip;
   }
-  ETN_TRY(cudaEventRecord(ck.ev[3], s.stream));
+  if (ck.timed) ETN_TRY(cudaEventRecord(ck.ev[3], s.stream));
+  ETN_TRY(cudaEventRecord(ck.done, s.stream));
   return 0;
 }
 
@@ -346,7 +353,7 @@ int issue_ragged(Device* d, Slot& s, Chunk& ck, Job* j, int64_t r0, const std::v
   int32_t* m_k = reinterpret_cast<int32_t*>(m_out + kMaxMetaRows);
   wait_for_meta(d, s);
   s.meta_seq = d->issued;
-  ETN_TRY(cudaEventRecord(ck.ev[0], s.stream));
+  if (ck.timed) ETN_TRY(cudaEventRecord(ck.ev[0], s.stream));
   const int64_t out0 = c->csum[r0];
   int64_t in_b = 0, r = r0, row = 0;
   for (const auto& b : blocks) {
@@ -366,16 +373,17 @@ int issue_ragged(Device* d, Slot& s, Chunk& ck, Job* j, int64_t r0, const std::v
   ETN_TRY(cudaMemcpyAsync(d_in_off, m_in, (size_t)rows * 8, cudaMemcpyHostToDevice, s.stream));
   ETN_TRY(cudaMemcpyAsync(d_out_off, m_out, (size_t)rows * 8, cudaMemcpyHostToDevice, s.stream));
   ETN_TRY(cudaMemcpyAsync(d_k, m_k, (size_t)rows * 4, cudaMemcpyHostToDevice, s.stream));
-  ETN_TRY(cudaEventRecord(ck.ev[1], s.stream));
+  if (ck.timed) ETN_TRY(cudaEventRecord(ck.ev[1], s.stream));
   if (int rc = etn_rt::run_rows(rows, INT64_MAX / 16, d_k, d_out_off, d_in_off, c->dtype, c->mode, s.d_in, s.d_out,
                                 s.stream))
     return rc;
   ck.has_kernel = true;
-  ETN_TRY(cudaEventRecord(ck.ev[2], s.stream));
+  if (ck.timed) ETN_TRY(cudaEventRecord(ck.ev[2], s.stream));
   const int64_t out_n = c->csum[r0 + rows] - out0;
   if (out_n > 0)
     ETN_TRY(cudaMemcpyAsync(c->hout + out0 * es, s.d_out, (size_t)(out_n * es), cudaMemcpyDeviceToHost, s.stream));
-  ETN_TRY(cudaEventRecord(ck.ev[3], s.stream));
+  if (ck.timed) ETN_TRY(cudaEventRecord(ck.ev[3], s.stream));
+  ETN_TRY(cudaEventRecord(ck.done, s.stream));
   return 0;
 }
 
@@ -440,6 +448,7 @@ void worker(Runtime* rt, Device* d) {
     ck.slot = (int)(d->issued % kSlots);
     ck.has_kernel = false;
     ck.failed = false;
+    ck.timed = rt->timing_every > 0 && d->issued % rt->timing_every == 0;
     Slot& s = d->slot[ck.slot];
     int rc = 0;
     segs.clear();
@@ -451,8 +460,8 @@ void worker(Runtime* rt, Device* d) {
       Job* j = take[0];
       const Call* c = j->call;
       const int64_t left = j->rows - j->cursor;
-      // a job is cut into ~2*kSlots chunks so that its D2H overlaps its own H2D
-      const int64_t target = std::min(kStageBytes, std::max((j->bytes + 2 * kSlots - 1) / (2 * kSlots), kMinChunkBytes));
+      // a job is cut into a few chunks so that its D2H overlaps its own H2D
+      const int64_t target = std::min(kStageBytes, std::max((j->bytes + rt->pieces - 1) / rt->pieces, kMinChunkBytes));
       int64_t n = 0;
       if (!c->kpr) {
         const int64_t w = c->kk * c->es, ip = up16(w);
@@ -485,7 +494,7 @@ void worker(Runtime* rt, Device* d) {
     // wake callers whose chunks have finished in the meantime, without blocking
     while (d->retired < d->issued) {
       const Chunk& o = d->rec[d->retired % kChunkRecs];
-      if (!o.failed && cudaEventQuery(o.ev[3]) != cudaSuccess) { cudaGetLastError(); break; }
+      if (!o.failed && cudaEventQuery(o.done) != cudaSuccess) { cudaGetLastError(); break; }
       retire_oldest(d);
     }
   }
@@ -501,8 +510,10 @@ Runtime::~Runtime() {
   const bool have_prev = cudaGetDevice(&prev) == cudaSuccess;
   for (auto& d : devs) {
     if (cudaSetDevice(d->dev) != cudaSuccess) { cudaGetLastError(); continue; }
-    for (Chunk& c : d->rec)
+    for (Chunk& c : d->rec) {
       for (cudaEvent_t e : c.ev) if (e) cudaEventDestroy(e);
+      if (c.done) cudaEventDestroy(c.done);
+    }
     for (Slot& s : d->slot) {
       if (s.stream) { cudaStreamSynchronize(s.stream); cudaStreamDestroy(s.stream); }
       if (s.d_in) cudaFree(s.d_in);
@@ -682,6 +693,8 @@ int etn_init(const int* device_ids, int n_devices) {
   auto rt = std::make_shared<Runtime>();
   rt->max_wait_us = env_i64("EMBED_GPU_MAX_WAIT_US", 0);
   rt->min_device_bytes = std::max<int64_t>(1, env_i64("EMBED_GPU_MIN_DEVICE_BYTES", 4 << 20));
+  rt->timing_every = env_i64("EMBED_GPU_TIMING", rt->timing_every);
+  rt->pieces = std::max<int64_t>(1, env_i64("EMBED_GPU_PIECES", rt->pieces));
   int rc = 0;
   for (int id : ids) {
     std::unique_ptr<Device> d(new Device());
@@ -695,9 +708,11 @@ int etn_init(const int* device_ids, int n_devices) {
       if (rc == 0 && (e = cudaMalloc(&s.d_meta, (size_t)kMetaBytes)) != cudaSuccess) rc = (int)e;
       if (rc == 0 && (e = cudaHostAlloc(&s.h_meta, (size_t)kMetaBytes, cudaHostAllocPortable)) != cudaSuccess) rc = (int)e;
     }
-    for (int i = 0; i < kChunkRecs && rc == 0; ++i)
+    for (int i = 0; i < kChunkRecs && rc == 0; ++i) {
       for (int v = 0; v < 4 && rc == 0; ++v)
         if ((e = cudaEventCreate(&d->rec[i].ev[v])) != cudaSuccess) rc = (int)e;
+      if (rc == 0 && (e = cudaEventCreateWithFlags(&d->rec[i].done, cudaEventDisableTiming)) != cudaSuccess) rc = (int)e;
+    }
     rt->devs.push_back(std::move(d));                 // owned by the runtime from here on, freed by ~Runtime
     if (rc) break;
   }
@@ -714,6 +729,7 @@ void etn_shutdown(void) {
     std::lock_guard<std::mutex> lock(g_mu);
     rt.swap(g_rt);
   }
+  etn_rt::release_json_staging();
   // Calls still in flight hold their own reference; the workers drain their queues and the
   // last reference (here or in the last waiter) joins them and frees the device memory.
 }

@@ -22,6 +22,9 @@ int run_dense(int64_t batch, int64_t D, int64_t k, int dtype, int mode, const vo
 int run_rows(int64_t batch, int64_t D, const int32_t* k_per_row, const int64_t* out_offsets,
              const int64_t* in_offsets, int dtype, int mode, const void* in, void* out, cudaStream_t s);
 
+// ---- etn_json.cpp
+void release_json_staging();              // frees the packer's reusable pinned buffer
+
 inline bool aligned_to(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
 
 }  // namespace etn_rt

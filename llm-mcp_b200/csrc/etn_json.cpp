@@ -23,6 +23,7 @@
 #include <atomic>
 #include <charconv>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <string.h>
 #include <mutex>
@@ -37,6 +38,7 @@ struct Scanner {
   const char* e;
   const char* p;
   bool ok = true;
+  bool escaped = false;    // the string last skipped held a backslash
 
   void ws() { while (p < e && (*p == ' ' || *p == '\t' || *p == '\n' || *p == '\r')) ++p; }
   bool fail() { ok = false; return false; }
@@ -45,44 +47,94 @@ struct Scanner {
   bool skip_string() {
     if (p >= e || *p != '"') return fail();
     ++p;
+    escaped = false;
     while (p < e) {
       const char c = *p++;
       if (c == '"') return true;
-      if (c == '\\') { if (p >= e) return fail(); ++p; }
+      if (c == '\\') { escaped = true; if (p >= e) return fail(); ++p; }
       else if ((unsigned char)c < 0x20) return fail();
     }
     return fail();
   }
-  // Same, and tells whether the string's raw bytes equal `key` (keys with escapes never match
-  // the plain ASCII keys looked for here; they are reported as a mismatch, which is right
-  // unless someone spells "data" as "data" — that is caught by the caller as a duplicate
-  // only if it matters, and otherwise passes through untouched).
+  // Same, for an object key, and tells whether the key equals `key` (plain ASCII) the way Go
+  // compares it: after unescaping.  A key spelled with escapes (a backslash-u-0061 for the
+  // second letter of "data", say) IS that key to the reference (handlers.go:2064, :2073 index
+  // the decoded map), so it is one here too.  An escape Go's decoder rejects fails the scan.
   bool string_is(const char* key, bool* same) {
     const char* s = p + 1;
     if (!skip_string()) return false;
-    const size_t n = (size_t)(p - 1 - s);
-    *same = n == strlen(key) && memcmp(s, key, n) == 0;
+    const char* t = p - 1;                          // closing quote
+    const size_t klen = strlen(key);
+    if (!escaped) {
+      *same = (size_t)(t - s) == klen && memcmp(s, key, klen) == 0;
+      return true;
+    }
+    size_t m = 0;                                   // characters of `key` matched so far
+    bool eq = true;
+    while (s < t) {
+      unsigned cp;
+      if (*s != '\\') { cp = (unsigned char)*s++; }
+      else {
+        if (++s >= t) return fail();
+        switch (*s++) {
+          case '"': cp = '"'; break;   case '\\': cp = '\\'; break; case '/': cp = '/'; break;
+          case 'b': cp = '\b'; break; case 'f': cp = '\f'; break;   case 'n': cp = '\n'; break;
+          case 'r': cp = '\r'; break; case 't': cp = '\t'; break;
+          case 'u': {
+            if (t - s < 4) return fail();
+            cp = 0;
+            for (int i = 0; i < 4; ++i) {
+              const char h = *s++;
+              cp = cp * 16 + (h >= '0' && h <= '9' ? h - '0' : h >= 'a' && h <= 'f' ? h - 'a' + 10 : h >= 'A' && h <= 'F' ? h - 'A' + 10 : 1u << 20);
+            }
+            if (cp >= (1u << 20)) return fail();     // not four hex digits
+            break;
+          }
+          default: return fail();
+        }
+      }
+      // the keys looked for are ASCII: any other code point (surrogates included) is a mismatch
+      if (eq && m < klen && cp == (unsigned char)key[m]) ++m; else eq = false;
+    }
+    *same = eq && m == klen;
     return true;
   }
+  // A number the reference cannot hold fails its whole decode (json.Decode into map[string]any
+  // parses EVERY number with strconv.ParseFloat(s, 64), handlers.go:2047-2050, and an overflow
+  // is an error -> 502), so it fails this scan too, wherever in the document it stands; the
+  // exact check only runs for tokens whose digit count plus exponent could reach 1e308.
   bool skip_number() {
     const char* s = p;
     if (p < e && *p == '-') ++p;
     if (p >= e) return fail();
+    const char* i0 = p;
     if (*p == '0') ++p;
     else if (*p >= '1' && *p <= '9') { while (p < e && *p >= '0' && *p <= '9') ++p; }
     else return fail();
+    const int64_t nint = p - i0;
     if (p < e && *p == '.') {
       ++p;
       if (p >= e || *p < '0' || *p > '9') return fail();
       while (p < e && *p >= '0' && *p <= '9') ++p;
     }
+    int64_t ex = 0;
     if (p < e && (*p == 'e' || *p == 'E')) {
       ++p;
+      const bool neg = p < e && *p == '-';
       if (p < e && (*p == '+' || *p == '-')) ++p;
       if (p >= e || *p < '0' || *p > '9') return fail();
-      while (p < e && *p >= '0' && *p <= '9') ++p;
+      while (p < e && *p >= '0' && *p <= '9') { if (ex < 100000) ex = ex * 10 + (*p - '0'); ++p; }
+      if (neg) ex = -ex;
     }
+    if (nint + ex > 308 && overflows(s, p)) return fail();
     return p > s;
+  }
+  static bool overflows(const char* s, const char* t) {
+    double d = 0;
+    auto r = std::from_chars(s, t, d);
+    if (r.ec != std::errc::result_out_of_range) return false;
+    std::string z(s, t);                            // out of range both ways: only overflow is an error in Go
+    return std::isinf(strtod(z.c_str(), nullptr));
   }
   bool skip_literal(const char* lit) {
     const size_t n = strlen(lit);
@@ -409,6 +461,15 @@ struct PinPool {
 
 }  // namespace
 
+namespace etn_rt {
+void release_json_staging() {                       // etn_shutdown: nothing of the library's stays pinned
+  std::lock_guard<std::mutex> lk(g_pin.mu);
+  if (g_pin.in) etn_free_pinned(g_pin.in);
+  g_pin.in = nullptr;
+  g_pin.cap = 0;
+}
+}  // namespace etn_rt
+
 extern "C" {
 
 int64_t etn_json_format_array(const double* v, int64_t n, char* buf, size_t cap) {
@@ -441,8 +502,12 @@ int64_t etn_json_parse_array(const char* text, size_t len, double* dst, int64_t 
     if (!sc.skip_number()) return ETN_ERR_JSON;
     if (n < max_n) {
       auto r = std::from_chars(s, sc.p, dst[n]);
-      if (r.ec == std::errc::result_out_of_range) return ETN_ERR_JSON;    // Go: "cannot unmarshal number ... into float64"
-      if (r.ec != std::errc() || r.ptr != sc.p) return ETN_ERR_JSON;
+      if (r.ec == std::errc::result_out_of_range) {
+        // overflow never gets here (skip_number refused it: Go's "cannot unmarshal number ... into
+        // float64"); underflow is no error in strconv.ParseFloat: the nearest value, 0 or a subnormal
+        std::string z(s, sc.p);
+        dst[n] = strtod(z.c_str(), nullptr);
+      } else if (r.ec != std::errc() || r.ptr != sc.p) return ETN_ERR_JSON;
     }
     ++n;
     sc.ws();

@@ -24,6 +24,8 @@ int main() {
       R"({"object":"list","data":[{"object":"embedding","index":0,"embedding":[0.1,-2.5e-3,3,4e10,5.5,6,7,8,9]},{"index":1,"embedding":[1,2]}],"model":"m","usage":{"prompt_tokens":3}})",
       R"({"data":[{"embedding":"AAAAPwAAAD8AAAA/AAAAPwAAAD8AAAA/"},{"embedding":null},"x",{"embedding":[1,"a",[2,3],{"b":4},5]}]})",
       R"( { "data" : [ { "embedding" : [ 1.0 , 2.0 ,	3.0 ] , "k\"]}" : "v\\" } ] , "z" : [ [ ] , { } ] } )",
+      // keys spelled with escapes (compared after unescaping, as Go does) and numbers at the edge of float64
+      R"({"d\u0061ta":[{"emb\u0065dding":[1e308,2E+307,3,4,5e-324],"\ud83d\ude00\/\b":1}],"us\u0061ge":{"prompt\u005ftokens":7e0},"big":17976931348623157e292})",
   };
   std::vector<char> out(1 << 16);
   int64_t stats[3];

@@ -29,11 +29,13 @@ def _init():
     # a worker that holds one small request waits up to 3 ms for company: makes the merging
     # of concurrent requests deterministic enough to assert on
     os.environ["EMBED_GPU_MAX_WAIT_US"] = "3000"
+    os.environ["EMBED_GPU_TIMING"] = "1"             # time every chunk: the histogram test counts them
     eg.shutdown()
     assert eg.init() >= 1
     yield
     eg.shutdown()
     os.environ.pop("EMBED_GPU_MAX_WAIT_US", None)
+    os.environ.pop("EMBED_GPU_TIMING", None)
 
 
 def _ulp(oracle, got, want, bar=2):

@@ -215,3 +215,48 @@ def test_prompt_tokens_like_the_handler():
     assert f(b'{"usage":{"prompt_tokens":-3.5}}') == -3
     with pytest.raises(eg.EtnError):
         f(b'{"usage":{"prompt_tokens":1}')
+
+
+def test_keys_spelled_with_escapes_are_the_keys_they_spell(oracle):
+    """Go compares object keys after unescaping (handlers.go:2064, :2073 index the decoded map), so
+    "d\\u0061ta" IS "data" to the reference — and to the packer: the vector is cut, a twin of
+    "data" written that way is a duplicate, and an escape Go rejects fails the scan."""
+    for body in (b'{"d\\u0061ta": [{"embedding": [1,2,3]}]}',
+                 b'{"data": [{"emb\\u0065dd\\u0069ng": [1,2,3]}]}',
+                 b'{"\\u0064\\u0061\\u0074\\u0061": [{"index": 0, "embedding": [1,2,3], "k\\"ey": 1, "\\u00e9": 2, "\\ud83d\\ude00": 3}]}'):
+        out, stats = eg.truncate_response_json(body, 2, renorm=False)
+        assert json.loads(out) == oracle.response_ref(body, 2, renorm=False) and stats["resliced_vectors"] == 1, body
+    for body in (b'{"data": [], "d\\u0061ta": [{"embedding": [1,2,3]}]}',
+                 b'{"data": [{"embedding": [1,2,3], "embeddin\\u0067": [4,5,6]}]}'):
+        with pytest.raises(eg.EtnError) as ei:
+            eg.truncate_response_json(body, 2, renorm=False)
+        assert ei.value.code == eg.ERR_JSON_DUP, body
+    for body in (b'{"d\\u00G1ta": 1}', b'{"d\\xta": 1}', b'{"data\\u00": 1}'):
+        with pytest.raises(eg.EtnError) as ei:
+            eg.truncate_response_json(body, 2, renorm=False)
+        assert ei.value.code == eg.ERR_JSON, body
+    assert eg.prompt_tokens(b'{"us\\u0061ge": {"prompt\\u005ftokens": 4}}') == 4
+    # near misses stay misses
+    body = b'{"dat\\u0061s": [{"embedding": [1,2,3]}], "Dat\\u0061": [{"embedding": [1,2,3]}]}'
+    assert eg.truncate_response_json(body, 2, renorm=False)[0] == body
+
+
+def test_numbers_outside_float64_fail_like_the_reference_decode():
+    """json.Decode into map[string]any parses every number of the body with ParseFloat(s, 64);
+    an overflow fails the request (handlers.go:2047-2050 -> 502).  TRUNCATE mode copies tokens
+    without parsing them, so the scan itself has to notice — wherever the token stands."""
+    for body in (b'{"data": [{"embedding": [1e999, 2, 3]}]}',
+                 b'{"data": [{"embedding": [1, 2, 3, -1e400]}]}',               # in the tail that is cut away
+                 b'{"data": [{"embedding": [1, 2, 3]}], "usage": {"x": 2e308}}',
+                 b'{"data": [{"embedding": [1, 2, 3]}], "big": ' + b"9" * 400 + b'}',
+                 b'{"data": [{"embedding": [0.0001e313, 2, 3]}]}'):
+        with pytest.raises(eg.EtnError) as ei:
+            eg.truncate_response_json(body, 2, renorm=False)
+        assert ei.value.code == eg.ERR_JSON, body
+    # the largest finite values, long digit strings that stay in range, and underflow (no error in Go) pass
+    ok = b'{"data": [{"embedding": [1.7976931348623157e308, ' + b"1" * 300 + b', 1e-999, 0.' + b"0" * 400 + b'1, 4]}]}'
+    out, _ = eg.truncate_response_json(ok, 4, renorm=False)
+    assert json.loads(out)["data"][0]["embedding"][0] == 1.7976931348623157e308 and len(json.loads(out)["data"][0]["embedding"]) == 4
+    buf = np.zeros(4)
+    assert eg.lib().etn_json_parse_array(b"[1e-999, 4.9e-324, 2e-324, -1e-400]", 35, buf.ctypes.data, 4) == 4
+    assert buf.tolist() == [0.0, 5e-324, 0.0, -0.0] and np.signbit(buf[3])
