@@ -271,6 +271,21 @@ ETN_API int64_t etn_json_parse_array(const char *text, size_t len, double *dst, 
  * ETN_ERR_JSON for NaN/Inf (which Go's encoder refuses). */
 ETN_API int64_t etn_json_format_array(const double *v, int64_t n, char *buf, size_t cap);
 
+/* The per-number work of the two calls above on the GPU, one thread per number — the kernels
+ * etn_json_truncate_response uses in ETN_TRUNCATE_RENORM mode, which ships the kept TEXT of the
+ * embedding arrays to the device, parses, renormalises and formats there, and brings text back
+ * (set ETN_JSON_GPU=0 to keep that work on the host cores).  All pointers are device memory.
+ * parse: token i is text[tok_begin[i] .. +tok_len[i]); out[i] receives its float64 and
+ * decided[i] = 1, or decided[i] = 0 when the fast algorithm (Eisel-Lemire) will not commit
+ * — then the caller asks etn_json_parse_array; it never answers wrongly.  Stands in for
+ * strconv.ParseFloat at handlers.go:2048.  format: v[i] is written at out + 32 * i exactly as
+ * encoding/json spells it (helpers.go:14), len[i] bytes (<= 25); v[i] must be finite. */
+ETN_API int etn_json_parse_tokens_device(const char *text, const int64_t *tok_begin,
+                                         const int32_t *tok_len, int64_t n, double *out,
+                                         uint8_t *decided, void *stream);
+ETN_API int etn_json_format_numbers_device(const double *v, int64_t n, char *out, int32_t *len,
+                                           void *stream);
+
 /* ---- observability ---- */
 
 /* Cumulative process-wide counters, to be exported as Prometheus counters beside

@@ -669,6 +669,17 @@ int wait_call(Call* c) {
 
 }  // namespace
 
+namespace etn_rt {
+int least_loaded_device() {
+  std::shared_ptr<Runtime> rt = runtime();
+  if (!rt || rt->devs.empty()) return -1;
+  Device* best = rt->devs[0].get();
+  for (auto& d : rt->devs)
+    if (d->load.load(std::memory_order_relaxed) < best->load.load(std::memory_order_relaxed)) best = d.get();
+  return best->dev;
+}
+}  // namespace etn_rt
+
 // =============================================================== C-ABI ======
 extern "C" {
 
@@ -730,6 +741,7 @@ void etn_shutdown(void) {
     rt.swap(g_rt);
   }
   etn_rt::release_json_staging();
+  etn_rt::json_gpu_shutdown();
   // Calls still in flight hold their own reference; the workers drain their queues and the
   // last reference (here or in the last waiter) joins them and frees the device memory.
 }

@@ -18,6 +18,7 @@
 // layout follows encoding/json's floatEncoder: 'f' form unless |x| < 1e-6 or |x| >= 1e21,
 // then 'e' form with "e-0d" shortened to "e-d".
 #include "../../include/embed_truncate_norm.h"
+#include "etn_internal.h"
 
 #include <algorithm>
 #include <atomic>
@@ -451,6 +452,12 @@ size_t format_go_float(double f, char* out) {
   return (size_t)(o - out);
 }
 
+// ETN_JSON_GPU=0 keeps the packer's number work on the host cores (read at use, like config.Getenv).
+bool gpu_text_enabled() {
+  const char* v = getenv("ETN_JSON_GPU");
+  return !(v && v[0] == '0');
+}
+
 // Reusable pinned staging for the rewrite (one per thread would be better still; handlers
 // call concurrently, so a mutex guards the shared one and overflow callers allocate their own).
 struct PinPool {
@@ -588,9 +595,25 @@ int64_t etn_json_truncate_response(const char* json, size_t len, int64_t dims, i
   double* vals = nullptr;
   float* vals32 = nullptr;
   void* own = nullptr;
+  // float64 arrays: first choice is the device text path (etn_json_gpu.cu) — the kept TEXT goes
+  // to the GPU, numbers are parsed, renormalised and formatted there, text comes back; if it is
+  // not available (workspace busy, shapes too large for shared memory, ETN_JSON_GPU=0) the host
+  // cores parse and format as before.
+  etn_rt::JsonGpuResult gres;
+  struct GpuRelease { etn_rt::JsonGpuResult* r; ~GpuRelease() { etn_rt::json_gpu_release(r); } } gpu_release{&gres};
+  bool text_on_gpu = false;
+  if (!gpu64.empty() && gpu_text_enabled()) {
+    std::vector<int64_t> tb(gpu64.size()), te(gpu64.size());
+    for (size_t g = 0; g < gpu64.size(); ++g) { tb[g] = spans[gpu64[g]].open + 1; te[g] = spans[gpu64[g]].cut; }
+    const int rc = etn_rt::json_renorm_gpu(json, tb.data(), te.data(), gpu64.size(), dims, &gres);
+    if (rc == 0) text_on_gpu = true;
+    else if (rc != etn_rt::kJsonGpuUnavailable && rc != ETN_ERR_NOT_INIT) return rc < 0 ? rc : -1000 - rc;
+  }
+  std::vector<size_t> host64;                        // float64 vectors parsed and formatted on the host
+  if (!text_on_gpu) host64 = gpu64;
   std::unique_lock<std::mutex> pin_lock(g_pin.mu, std::defer_lock);
-  if (!gpu64.empty() || !gpu32.empty()) {
-    const size_t need64 = gpu64.size() * (size_t)dims * sizeof(double);
+  if (!host64.empty() || !gpu32.empty()) {
+    const size_t need64 = host64.size() * (size_t)dims * sizeof(double);
     const size_t need = need64 + gpu32.size() * (size_t)dims * sizeof(float);
     if (pin_lock.try_lock()) {
       if (g_pin.cap < need) {
@@ -605,8 +628,8 @@ int64_t etn_json_truncate_response(const char* json, size_t len, int64_t dims, i
     if (!vals) return -1000 - 2;                   // cudaErrorMemoryAllocation
     vals32 = (float*)((char*)vals + need64);
     std::atomic<int64_t> parse_err{0};
-    parallel_for(gpu64.size(), 8, [&](size_t g) {
-      const Span& s = spans[gpu64[g]];
+    parallel_for(host64.size(), 8, [&](size_t g) {
+      const Span& s = spans[host64[g]];
       const int64_t n = etn_json_parse_array(json + s.open, (size_t)(s.close - s.open), vals + g * dims, dims);
       if (n < 0) parse_err.store(n);
     });
@@ -616,17 +639,17 @@ int64_t etn_json_truncate_response(const char* json, size_t len, int64_t dims, i
     });
     // prefix-only buffers: D == k == dims, renormalised in place through the host path
     int rc = 0;
-    if (!gpu64.empty())
-      rc = embed_truncate_norm_host((int64_t)gpu64.size(), dims, dims, ETN_F64, ETN_TRUNCATE_RENORM, vals, 0, vals, n_devices);
+    if (!host64.empty())
+      rc = embed_truncate_norm_host((int64_t)host64.size(), dims, dims, ETN_F64, ETN_TRUNCATE_RENORM, vals, 0, vals, n_devices);
     if (rc == 0 && !gpu32.empty())
       rc = embed_truncate_norm_host((int64_t)gpu32.size(), dims, dims, ETN_F32, ETN_TRUNCATE_RENORM, vals32, 0, vals32, n_devices);
     if (rc != 0) { if (own) etn_free_pinned(own); return rc < 0 ? rc : -1000 - rc; }
   }
   // format the renormalised float64 vectors on all cores, then splice sequentially
   const size_t fstride = (size_t)dims * 34 + 2;
-  std::vector<char> ftext(gpu64.size() * fstride);
-  std::vector<int64_t> flen(gpu64.size());
-  parallel_for(gpu64.size(), 8, [&](size_t g) {
+  std::vector<char> ftext(host64.size() * fstride);
+  std::vector<int64_t> flen(host64.size());
+  parallel_for(host64.size(), 8, [&](size_t g) {
     flen[g] = etn_json_format_array(vals + g * dims, dims, ftext.data() + g * fstride, fstride);
   });
   // splice
@@ -663,9 +686,9 @@ int64_t etn_json_truncate_response(const char* json, size_t len, int64_t dims, i
       o += enc;
       out[o++] = '"';
     } else if (g64 < gpu64.size() && gpu64[g64] == i) {
-      const int64_t w = flen[g64];
+      const int64_t w = text_on_gpu ? (int64_t)gres.len[g64] : flen[g64];
       if (w < 0) { if (own) etn_free_pinned(own); return w; }     // NaN/Inf: Go's encoder would refuse too
-      fits = put(ftext.data() + g64 * fstride, (size_t)w);
+      fits = put(text_on_gpu ? gres.text + g64 * gres.stride : ftext.data() + g64 * fstride, (size_t)w);
       if (!fits) break;
       ++g64;
       if (stats) ++stats[0];

@@ -40,6 +40,7 @@ EXPORTS = (
     "etn_get_counters", "etn_counter_name",
     "embed_truncate_norm_gather", "embed_truncate_norm_ragged_host", "etn_shard_ragged", "etn_submit_host", "etn_wait",
     "etn_note_fallback", "etn_get_histogram", "etn_histogram_name", "etn_histogram_help", "etn_raw_copy_seconds",
+    "etn_json_parse_tokens_device", "etn_json_format_numbers_device",
 )
 
 
@@ -102,6 +103,8 @@ def lib() -> ctypes.CDLL:
         L.etn_histogram_help.argtypes = [ci]
         L.etn_histogram_help.restype = ctypes.c_char_p
         L.etn_raw_copy_seconds.argtypes = [vp, vp, ctypes.c_size_t, ci, ci, vp]
+        L.etn_json_parse_tokens_device.argtypes = [vp, vp, vp, i64, vp, vp, vp]
+        L.etn_json_format_numbers_device.argtypes = [vp, i64, vp, vp, vp]
         _lib = L
     return _lib
 

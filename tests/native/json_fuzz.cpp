@@ -3,11 +3,17 @@
 // is compiled in directly, the CUDA-side entry points it calls are stubbed (TRUNCATE mode
 // never reaches them), and a few thousand byte-level mutations of provider-like responses are
 // pushed through.  Any out-of-bounds access or UB aborts the process.
+#define ETN_NO_CUDA
 #include "../../llm-mcp_b200/csrc/etn_json.cpp"
 
 #include <cstdio>
 #include <cstdlib>
 #include <random>
+
+namespace etn_rt {   // the device text path is not part of this build: "use the host path"
+int json_renorm_gpu(const char*, const int64_t*, const int64_t*, size_t, int64_t, JsonGpuResult*) { return kJsonGpuUnavailable; }
+void json_gpu_release(JsonGpuResult*) {}
+}  // namespace etn_rt
 
 extern "C" {
 void* etn_alloc_pinned(size_t n) { return malloc(n); }

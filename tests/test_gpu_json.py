@@ -1,0 +1,148 @@
+"""-m gpu tests of the JSON packer's device path (llm-mcp_b200/csrc/etn_json_gpu.cu,
+etn_numfmt.cuh): the numbers of the kept prefixes are parsed, renormalised and formatted on the
+GPU.  Bar: byte-identical with the host path (std::from_chars / std::to_chars, the guarantees
+of strconv.ParseFloat / AppendFloat that encoding/json uses at handlers.go:2048 and
+helpers.go:14) and with the oracle's Go spelling."""
+import ctypes
+import json
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+if not torch.cuda.is_available():
+    pytest.skip("no CUDA device", allow_module_level=True)
+
+from llm_mcp_b200 import embedgpu as eg  # noqa: E402
+from tests.gpu_util import to_dev  # noqa: E402
+from tests.test_json_packer import GO_KNOWN  # noqa: E402
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _init():
+    assert eg.init() >= 1
+    yield
+    eg.shutdown()
+
+
+def _random_doubles(n, seed):
+    rng = np.random.default_rng(seed)
+    bits = rng.integers(0, 2 ** 64, size=n, dtype=np.uint64)
+    v = bits.view(np.float64).copy()
+    v = v[np.isfinite(v)]
+    emb = rng.standard_normal(n) * 0.04
+    ints = rng.integers(-10 ** 15, 10 ** 15, size=n // 4).astype(np.float64)
+    edge = np.array([0.0, -0.0, 1e-6, 9.999999999999999e-7, 1e21, 999999999999999934463.0, 5e-324, 1.7976931348623157e308,
+                     2.2250738585072014e-308, 0.1, 0.3, 1 / 3, 100.0, 1e22, 123456789.125] + [x for x, _ in GO_KNOWN])
+    return np.concatenate([v, emb, ints, edge, -edge])
+
+
+def _host_format(v):
+    buf = ctypes.create_string_buffer(40)
+    out = []
+    for x in v:
+        a = np.array([x])
+        n = eg.lib().etn_json_format_array(a.ctypes.data, 1, buf, 40)
+        assert n > 2
+        out.append(buf.raw[1:n - 1])
+    return out
+
+
+def test_device_format_equals_host_format_and_go_spelling(oracle):
+    v = _random_doubles(25000, 1)
+    d_v = to_dev(v)
+    d_out = torch.zeros(len(v) * 32, dtype=torch.uint8, device="cuda")
+    d_len = torch.zeros(len(v), dtype=torch.int32, device="cuda")
+    eg.check(eg.lib().etn_json_format_numbers_device(d_v.data_ptr(), len(v), d_out.data_ptr(), d_len.data_ptr(), None), "format")
+    torch.cuda.synchronize()
+    text, lens = d_out.cpu().numpy().reshape(-1, 32), d_len.cpu().numpy()
+    got = [text[i, :lens[i]].tobytes() for i in range(len(v))]
+    want = _host_format(v)
+    bad = [(float(x), g, w) for x, g, w in zip(v, got, want) if g != w]
+    assert not bad, bad[:5]
+    for x, g in list(zip(v, got))[::97]:                       # and the oracle's restatement of encoding/json
+        assert g.decode() == oracle.go_format_float(float(x)), x
+    spelled = dict(zip((float(x) for x in v), got))
+    for x, want_text in GO_KNOWN:                              # Go's documented spellings
+        assert spelled[x].decode() == want_text, x
+    assert lens.max() <= 25
+
+
+def test_device_parse_equals_host_parse():
+    v = _random_doubles(25000, 2)
+    toks = _host_format(v)                                     # shortest spellings ...
+    rng = np.random.default_rng(3)
+    toks += [("%.17g" % x).encode() for x in v[::3]]           # ... 17 digits ...
+    toks += [("%.*e" % (int(rng.integers(0, 19)), x)).encode() for x in v[::5]]
+    toks += [b"1e999", b"-1e999", b"12345678901234567890", b"0.12345678901234567891", b"4.9e-324", b"1e-999", b"1E5", b"0e0", b"-0.0"]
+    toks = [t for t in toks if b"n" not in t and b"i" not in t]
+    blob = b",".join(toks)
+    beg = np.cumsum([0] + [len(t) + 1 for t in toks[:-1]]).astype(np.int64)
+    ln = np.array([len(t) for t in toks], dtype=np.int32)
+    d_text = to_dev(np.frombuffer(blob, dtype=np.uint8).copy())
+    d_beg, d_len = to_dev(beg), to_dev(ln)
+    d_out = torch.zeros(len(toks), dtype=torch.float64, device="cuda")
+    d_ok = torch.zeros(len(toks), dtype=torch.uint8, device="cuda")
+    eg.check(eg.lib().etn_json_parse_tokens_device(d_text.data_ptr(), d_beg.data_ptr(), d_len.data_ptr(), len(toks), d_out.data_ptr(),
+                                                   d_ok.data_ptr(), None), "parse")
+    torch.cuda.synchronize()
+    got, ok = d_out.cpu().numpy(), d_ok.cpu().numpy().astype(bool)
+    want = np.zeros(len(toks))
+    host_ok = np.zeros(len(toks), dtype=bool)
+    one = np.zeros(1)
+    for i, t in enumerate(toks):
+        arr = b"[" + t + b"]"
+        host_ok[i] = eg.lib().etn_json_parse_array(arr, len(arr), one.ctypes.data, 1) == 1
+        want[i] = one[0]
+    assert not (ok & ~host_ok).any()                           # never answers what the host refuses (overflow)
+    both = ok & host_ok
+    assert np.array_equal(got[both].view(np.uint64), want[both].view(np.uint64))
+    assert both.mean() > 0.97                                  # the fall-back is the rare case
+
+
+def _body(x, sep=(", ", ": "), indent=None):
+    return json.dumps({"object": "list", "data": [{"object": "embedding", "index": i, "embedding": r} for i, r in enumerate(x)],
+                       "usage": {"prompt_tokens": 4}}, separators=sep, indent=indent).encode()
+
+
+def test_response_rewrite_on_the_gpu_is_byte_identical_to_the_host_path(oracle):
+    rng = np.random.default_rng(9)
+    x = [list(map(float, r)) for r in oracle.fill(1, 48, 2048, np.float64)]
+    x += [list(map(float, rng.standard_normal(2048) * 10.0 ** rng.integers(-8, 8))) for _ in range(8)]
+    x[3][5] = 0.0; x[3][6] = -0.0; x[4] = [0.0] * 2048                        # zeros; an all-zero prefix is copied
+    x[5][:4] = [1e-300, -2.5e300, 123456789012345680000.0, 5e-324]             # scaling path of the renorm kernel, subnormal in
+    x[6] = x[6][:700]                                                          # shorter than dims: left whole
+    for sep, indent in (((", ", ": "), None), ((",", ":"), None), ((" ,\n", " : "), 1)):
+        body = _body(x, sep, indent)
+        os.environ["ETN_JSON_GPU"] = "0"
+        host, hs = eg.truncate_response_json(body, 1024, renorm=True)
+        os.environ["ETN_JSON_GPU"] = "1"
+        before = eg.counters()["llmcore_embed_gpu_kernel_launches_total"]
+        dev, ds = eg.truncate_response_json(body, 1024, renorm=True)
+        launches = eg.counters()["llmcore_embed_gpu_kernel_launches_total"] - before
+        os.environ.pop("ETN_JSON_GPU")
+        assert dev == host and ds == hs
+        assert launches == 3                                   # parse, renormalise, format: one launch each
+        want = oracle.response_ref(body, 1024, renorm=True)
+        got = json.loads(dev)
+        for a, b in zip(got["data"], want["data"]):
+            d, i = oracle.max_ulp(np.array(a["embedding"]), np.array(b["embedding"], dtype=np.float64))
+            assert 0 <= d <= 2, (d, i)
+
+
+def test_numbers_the_fast_parser_declines_are_redone_by_the_host(oracle):
+    x = [list(map(float, r)) for r in oracle.fill(2, 6, 300, np.float64)]
+    body = _body(x, (",", ":"))
+    # 25 significant digits in vector 1, a half-way case in vector 4: Eisel-Lemire says "ask the host"
+    body = body.replace(b'"index":1,"embedding":[', b'"index":1,"embedding":[0.1234567890123456789012345,', 1)
+    body = body.replace(b'"index":4,"embedding":[', b'"index":4,"embedding":[9007199254740993,', 1)
+    os.environ["ETN_JSON_GPU"] = "0"
+    host, _ = eg.truncate_response_json(body, 128, renorm=True)
+    os.environ["ETN_JSON_GPU"] = "1"
+    dev, _ = eg.truncate_response_json(body, 128, renorm=True)
+    os.environ.pop("ETN_JSON_GPU")
+    assert dev == host
+    assert json.loads(dev) == json.loads(host)
