@@ -129,7 +129,7 @@ ETN_API int embed_truncate_norm_gather(int64_t batch, const int64_t *in_offsets,
  *                                histograms (default 16; 1 = every chunk, 0 = none: the four
  *                                timestamped records cost a small request a quarter of its time)
  *   EMBED_GPU_PIECES             chunks a lone request is cut into so that its D2H overlaps
- *                                its own H2D (default 4) */
+ *                                its own H2D (default 16, but no chunk under 2 MiB or over a slot) */
 ETN_API int etn_init(const int *device_ids, int n_devices);
 
 /* Releases what etn_init created (main.go:118-122, graceful shutdown). */

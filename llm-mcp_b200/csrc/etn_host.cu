@@ -53,7 +53,7 @@ constexpr int kSlots = 4;                           // chunks in flight per devi
 constexpr int64_t kStageBytes = 64ll << 20;         // staging per slot, each direction
 constexpr int64_t kMaxMetaRows = 256 << 10;         // rows of a chunk that needs per-row metadata
 constexpr int64_t kMetaBytes = kMaxMetaRows * (8 + 8 + 4);
-constexpr int64_t kMinChunkBytes = 512 << 10;       // below this a chunk is all submission latency
+constexpr int64_t kMinChunkBytes = 2 << 20;         // smaller chunks cost more in submission than their overlap buys
 constexpr int64_t kSmallJobBytes = 16ll << 20;      // jobs up to this size may share a chunk
 constexpr size_t kMaxJobsPerChunk = 256;
 constexpr int64_t kShortRun = 16;                   // ragged: runs shorter than this absorb their neighbours
@@ -154,9 +154,11 @@ struct Runtime {
   int64_t min_device_bytes = 4 << 20;
   // Measured (profiles/r02_latency.txt): the four timestamped event records cost a 64-row request
   // 20 of its 73 us and a C1 request 50 of 384 us, and four pieces beat eight once every piece
-  // carries its own completion event.  Hence: every 16th chunk is timed, four pieces.
+  // carries its own completion event.  Hence: every 16th chunk is timed, and a job is cut into
+  // 16 chunks of at least 2 MiB and at most one slot (C1: four chunks of 2 MiB; 512 MiB: sixteen
+  // of 32 MiB, so the un-overlapped first H2D and last D2H stay a small part of the whole).
   int64_t timing_every = 16;       // EMBED_GPU_TIMING: time every n-th staged chunk (1 = all, 0 = none)
-  int64_t pieces = kSlots;         // EMBED_GPU_PIECES: chunks a lone job is cut into
+  int64_t pieces = 16;             // EMBED_GPU_PIECES: chunks a lone job is cut into (floor 2 MiB each)
   std::atomic<uint32_t> rr{0};
   ~Runtime();
 };

@@ -9,7 +9,7 @@ pi, po = eg.PinnedBuffer(1024 * D * 8), eg.PinnedBuffer(1024 * k * 8)
 x, y = pi.array((1024, D), np.float64), po.array((1024, k), np.float64)
 x[:, :k] = 0.01
 L = eg.lib()
-for timing, pieces in ((1, 8), (0, 8), (4, 8), (1, 4), (0, 4), (0, 2), (0, 1), (0, 16)):
+for timing, pieces in ((16, 16), (1, 16), (0, 16), (0, 4), (0, 1)):
     os.environ["EMBED_GPU_TIMING"], os.environ["EMBED_GPU_PIECES"] = str(timing), str(pieces)
     eg.init([0])
     out = []
