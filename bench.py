@@ -548,7 +548,10 @@ def multi_gpu_blocks(torch, dist, eg, args, rank, local_rank, world, peak):
     torch.cuda.empty_cache()
     barrier()
 
-    # ---- the library's own sharding: one process, N device workers
+    # ---- the library's own sharding: one process, N device workers.  The other ranks wait on the
+    # rendezvous store (a socket), not in a collective: no kernel of theirs spins on a GPU and no
+    # host thread of theirs polls while rank 0 has the box to itself.
+    store = dist.distributed_c10d._get_default_store()
     if rank == 0:
         try:
             rows_per, Dc, kc = 131072, 4096, 1024
@@ -575,6 +578,10 @@ def multi_gpu_blocks(torch, dist, eg, args, rank, local_rank, world, peak):
             out["e2e_inprocess"] = res
         except Exception as e:  # noqa: BLE001
             out["e2e_inprocess"] = {"error": repr(e)[:200]}
+        store.set("etn_e2e_inprocess_done", "1")
+    else:
+        import datetime
+        store.wait(["etn_e2e_inprocess_done"], datetime.timedelta(minutes=15))
     barrier()
     return out
 

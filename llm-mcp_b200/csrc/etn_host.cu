@@ -159,7 +159,6 @@ struct Runtime {
   // of 32 MiB, so the un-overlapped first H2D and last D2H stay a small part of the whole).
   int64_t timing_every = 16;       // EMBED_GPU_TIMING: time every n-th staged chunk (1 = all, 0 = none)
   int64_t pieces = 16;             // EMBED_GPU_PIECES: chunks a lone job is cut into (floor 2 MiB each)
-  std::atomic<uint32_t> rr{0};
   ~Runtime();
 };
 
@@ -601,9 +600,12 @@ int submit(int64_t batch, int64_t D, int64_t k, const int32_t* kpr, int dtype, i
 
   // how many devices, and which: one more device per min_device_bytes, the least loaded first
   int nd = (int)std::max<int64_t>(1, std::min<int64_t>({(int64_t)n_devices, batch, total / std::max<int64_t>(1, rt->min_device_bytes)}));
+  // Least loaded first; among equally loaded ones the lowest ordinal, NOT a rotation: a lone
+  // caller then keeps hitting the same worker, which is still polling its queue, instead of
+  // waking a sleeping one on every call (measured on the 8-GPU box: p99 of a C1 request 1.06 ms
+  // with a rotating start, against a p50 of 0.19 ms).  Concurrent callers spread through the load.
   std::vector<int> order((size_t)ndev);
   std::iota(order.begin(), order.end(), 0);
-  std::rotate(order.begin(), order.begin() + (rt->rr.fetch_add(1, std::memory_order_relaxed) % (uint32_t)ndev), order.end());
   std::stable_sort(order.begin(), order.end(), [&](int a, int b) {
     return rt->devs[a]->load.load(std::memory_order_relaxed) < rt->devs[b]->load.load(std::memory_order_relaxed);
   });

@@ -38,6 +38,17 @@ def _init():
     os.environ.pop("EMBED_GPU_TIMING", None)
 
 
+@pytest.fixture
+def one_device():
+    """Requests only queue up behind each other — and get merged — when they meet on one device;
+    with several devices bound the library spreads them instead.  The merging tests bind one."""
+    eg.shutdown()
+    assert eg.init([0]) == 1
+    yield
+    eg.shutdown()
+    assert eg.init() >= 1
+
+
 def _ulp(oracle, got, want, bar=2):
     d, i = oracle.max_ulp(got, want)
     assert 0 <= d <= bar, (d, i)
@@ -114,7 +125,7 @@ def test_ragged_host_large_multi_chunk_sharded_by_kept_bytes(oracle):
 
 
 # ------------------------------------------------------------------- coalescing ----
-def test_concurrent_small_requests_share_launches(oracle):
+def test_concurrent_small_requests_share_launches(oracle, one_device):
     """Sixteen C1-like requests submitted together: the worker merges the queued ones into
     shared chunks (one H2D set, ONE kernel, one D2H set) — same k for all, so the dense
     kernel runs on the merged matrix."""
@@ -135,7 +146,7 @@ def test_concurrent_small_requests_share_launches(oracle):
     assert sum(h1["counts"][1:]) - sum(h0["counts"][1:]) >= 1
 
 
-def test_concurrent_requests_with_different_k_and_D_share_a_launch(oracle):
+def test_concurrent_requests_with_different_k_and_D_share_a_launch(oracle, one_device):
     """Requests of different models and different `dimensions` (handlers.go:1874-1877) in one
     launch: per-row metadata and the gathering page-ring kernel.  Odd k and pitched rows too."""
     shapes = [(300, 768, 256), (64, 4096, 1024), (500, 1024, 100), (33, 3072, 257), (200, 768, 768), (90, 1536, 5000),
