@@ -227,8 +227,9 @@ int launch_ring(const void* in, void* out, int64_t batch, int64_t D, int64_t k_d
 //   16-byte tileable, 8 KiB - 112 KiB:                rows_wide (row in shared memory, whole block)
 //   32-byte tileable, <= 8 KiB:                       rows_reg with 256-bit accesses
 //   16-byte tileable, <= 8 KiB:                       rows_reg with 128-bit accesses
-//   16-byte aligned input rows, odd k, <= 8 KiB:      rows_ring (staged rounded up, element-wise)
-//   anything else:                                    rows_general
+//   odd k on aligned rows, or float64 rows off the 16-byte grid, < 8 KiB:
+//                                                     rows_ring (aligned span staged, element-wise)
+//   anything else (float32 rows off the grid, longer rows of that kind): rows_general
 // Truncation moves bytes, so one instantiation (T = float) serves both element types.
 // ALIAS = 1 (out == in): the register kernels load through the coherent path (no ld.global.nc).
 template <typename T, int MODE, int ALIAS>
@@ -288,9 +289,16 @@ int launch_dense(const void* in, void* out, int64_t batch, int64_t D, int64_t kk
     if (nv <= 8) return launch_reg<TT, 16, 8, 1, 32, MODE, MB4, ALIAS>(in, out, batch, in_pitch, nvec, W, s);
     return launch_reg<TT, 16, 16, 1, 32, MODE, MB8, ALIAS>(in, out, batch, in_pitch, nvec, W, s);
   }
-  // prefix not 16-byte tileable (odd k) but 16-byte aligned input rows: staged through the ring
-  if (aligned_to(in, 16) && in_pitch % 16 == 0 && k_bytes <= 8192 - 16)
-    return launch_ring<T, MODE>(in, out, batch, D, kk, nullptr, nullptr, nullptr, s);
+  // prefix not 16-byte tileable (odd k) or rows off the 16-byte grid (odd D, shifted base): the
+  // aligned span around every prefix is staged through the page ring
+  // Measured (profiles/r02_offgrid.txt, 1,000,000 x 771 -> 257 and 500,000 x 4097 -> 1024): off the
+  // grid the ring wins for float64 (5.6 / 5.0 TB/s against 5.1 / 5.0 in the general kernel) and
+  // loses for float32, whose 1 KiB rows are all per-row bookkeeping there (3.7 against 4.8 TB/s).
+  {
+    const bool on_grid = aligned_to(in, 16) && in_pitch % 16 == 0;
+    if (k_bytes <= 8192 - 32 && (on_grid || sizeof(T) == 8))
+      return launch_ring<T, MODE>(in, out, batch, D, kk, nullptr, nullptr, nullptr, s);
+  }
   return launch_general<T, MODE>(in, out, batch, D, kk, nullptr, nullptr, nullptr, s);
 }
 
@@ -303,8 +311,6 @@ template <typename T, int MODE>
 int launch_ring(const void* in, void* out, int64_t batch, int64_t D, int64_t k_dense, const int32_t* k_per_row,
                 const int64_t* out_offsets, const int64_t* in_offsets, cudaStream_t s) {
   const int64_t in_pitch = D * (int64_t)sizeof(T);
-  if (!(aligned_to(in, 16) && (in_offsets || in_pitch % 16 == 0)))
-    return launch_general<T, MODE>(in, out, batch, D, k_dense, k_per_row, out_offsets, in_offsets, s);
   constexpr int NCW = 4;
   constexpr size_t smem = (size_t)NCW * 8192 + (size_t)NCW * 8 * 8 + (size_t)NCW * 8 * 3 * 4;
   // 16 pages per warp, register budget of 4 resident blocks (6 still fit), 4 rows per warp: tools/tune ring,

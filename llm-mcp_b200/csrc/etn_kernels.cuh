@@ -554,8 +554,9 @@ rows_bulk_kernel(const char* in, char* out, int64_t batch,
 // rolled passes, so the instruction count follows the row's real length and the kernel needs
 // few registers (a register-resident version sized for the longest row ran 777 instructions
 // per row at 12 warps per SM and was issue-bound at 3.1-3.7 TB/s).
-// Only the input rows have to be 16-byte aligned: a prefix that is not a multiple of 16
-// bytes is staged rounded up and processed element-wise.  Dense batches with such a k use
+// Nothing but element alignment is required of the input: a prefix that is not a multiple of
+// 16 bytes, or a row that starts off a 16-byte boundary (odd D, shifted base), is staged as the
+// 16-byte aligned span around it and processed element-wise.  Dense batches of that kind use
 // this kernel too (k_per_row == out_offsets == nullptr).  A row longer than the ring takes
 // general_row.
 template <typename T, int NCW, int MODE, int P = 16, int MINB = 6>
@@ -584,21 +585,28 @@ rows_ring_kernel(const char* in, char* out, int64_t batch,
   __syncthreads();
   pdl_prologue();
 
-  // Bytes of row `row` to stage: its prefix rounded up to 16 (the input rows are 16-byte
-  // aligned and pitched, so the round-up stays inside the row), or 0 when it does not fit
-  // the ring.  k_per_row == nullptr: every row keeps k_dense; out_offsets == nullptr: dense.
+  // Bytes of row `row` to stage: the 16-byte aligned span that covers its prefix — `lead` bytes
+  // of whatever precedes the row when it starts off a 16-byte boundary, up to 15 bytes behind
+  // its last kept element — or 0 when that span does not fit the ring or would reach outside
+  // the caller's matrix (first / last row of an unaligned one; with in_offsets the caller
+  // vouches for aligned row starts and for 15 readable bytes behind every row).
+  // k_per_row == nullptr: every row keeps k_dense; out_offsets == nullptr: dense.
   // in_offsets != nullptr: row `row` starts at element in_offsets[row] of `in` (rows gathered
   // from several requests into one launch) instead of at row * in_pitch.
   auto row_src = [&](int64_t row) -> const char* {
     return in_offsets ? in + in_offsets[row] * (int64_t)sizeof(T) : in + row * in_pitch;
   };
-  auto row_plan = [&](int64_t row, char*& dst, int64_t& kr) -> uint32_t {
+  const char* const in_end = in + batch * in_pitch;
+  auto row_plan = [&](int64_t row, char*& dst, int64_t& kr, int& lead) -> uint32_t {
     kr = k_per_row ? (int64_t)k_per_row[row] : k_dense;
     if (kr > D) kr = D;
     const int64_t kb = kr * (int64_t)sizeof(T);
     dst = out + (out_offsets ? out_offsets[row] : row * kr) * (int64_t)sizeof(T);
-    const int64_t staged = (kb + 15) & ~(int64_t)15;
-    return (kb > 0 && staged <= (int64_t)RING) ? (uint32_t)staged : 0u;
+    const char* src = row_src(row);
+    lead = (int)(reinterpret_cast<uintptr_t>(src) & 15);
+    const int64_t staged = (lead + kb + 15) & ~(int64_t)15;
+    const bool inside = in_offsets || (src - lead >= in && src - lead + staged <= in_end);
+    return (kb > 0 && staged <= (int64_t)RING && inside) ? (uint32_t)staged : 0u;
   };
 
   uint64_t policy;
@@ -611,8 +619,8 @@ rows_ring_kernel(const char* in, char* out, int64_t batch,
   int head_page = 0, used = 0, inflight = 0;
   auto issue_more = [&]() {
     while (head_row < end && inflight < R) {
-      char* d; int64_t kr;
-      const uint32_t nb = row_plan(head_row, d, kr);
+      char* d; int64_t kr; int lead;
+      const uint32_t nb = row_plan(head_row, d, kr, lead);
       const int slot = (int)((head_row - first) % R);
       if (nb == 0) {
         my_meta[slot * 3 + 1] = 0; my_meta[slot * 3 + 2] = 0;
@@ -622,7 +630,7 @@ rows_ring_kernel(const char* in, char* out, int64_t batch,
         int pos = head_page, waste = 0;
         if (pos + need > P) { waste = P - pos; pos = 0; }
         if (used + waste + need > P) break;
-        bulk_load_row(smem_u32(my_ring + pos * PAGE), row_src(head_row), nb, bar0 + 8u * slot, policy);
+        bulk_load_row(smem_u32(my_ring + pos * PAGE), row_src(head_row) - lead, nb, bar0 + 8u * slot, policy);
         my_meta[slot * 3] = pos; my_meta[slot * 3 + 1] = (int)nb; my_meta[slot * 3 + 2] = waste + need;
         used += waste + need;
         head_page = pos + need == P ? 0 : pos + need;
@@ -639,8 +647,8 @@ rows_ring_kernel(const char* in, char* out, int64_t batch,
     const int pos = my_meta[slot * 3];
     const uint32_t row_bytes = (uint32_t)my_meta[slot * 3 + 1];
     const int held = my_meta[slot * 3 + 2];
-    char* dst; int64_t kr;
-    row_plan(row, dst, kr);
+    char* dst; int64_t kr; int lead;
+    row_plan(row, dst, kr, lead);
     if (row_bytes == 0) {                               // warp-uniform: odd row, nothing staged
       __syncwarp();
       if (lane == 0) { --inflight; issue_more(); }
@@ -652,12 +660,14 @@ rows_ring_kernel(const char* in, char* out, int64_t batch,
     const int nvec16 = (int)(row_bytes >> 4);
     const uint4* src = reinterpret_cast<const uint4*>(my_ring + pos * PAGE);
     uint4* dst4 = reinterpret_cast<uint4*>(dst);
-    const bool vec_ok = ((kr * (int64_t)sizeof(T)) % 16 == 0) && (reinterpret_cast<uintptr_t>(dst) % 16) == 0;
+    const bool vec_ok = lead == 0 && ((kr * (int64_t)sizeof(T)) % 16 == 0) && (reinterpret_cast<uintptr_t>(dst) % 16) == 0;
 
     if (!vec_ok) {
-      // odd k, or an output row that is not 16-byte aligned: same two passes over the staged
-      // row, element by element (coalesced 4/8-byte accesses)
-      const T* xs = reinterpret_cast<const T*>(src);
+      // odd k, a row that starts off the 16-byte grid, or an output row that does: same two
+      // passes over the staged row, element by element (coalesced 4/8-byte accesses).  (A variant
+      // that kept both passes on 16-byte vectors — masked sum, word-shifted stores — ran 609
+      // instructions per 1 KiB row and was slower: profiles/r02_offgrid.txt.)
+      const T* xs = reinterpret_cast<const T*>(reinterpret_cast<const unsigned char*>(src) + lead);
       T* y = reinterpret_cast<T*>(dst);
       const int n = (int)kr;
       if constexpr (MODE == kModeTruncate) {
