@@ -1,5 +1,8 @@
-"""Summarises a .ncu-rep (raw page CSV) into a markdown table under profiles/."""
-import csv, subprocess, sys
+"""Summarises a .ncu-rep (raw page CSV) into a markdown table under profiles/.
+    python tools/ncu_summary.py report.ncu-rep out.md "title" [traffic.json key]
+With the last two arguments the DRAM bytes (read + write) of the first launch are stored under
+`key` in traffic.json — the figure bench.py republishes as roofline.traffic."""
+import csv, json, os, subprocess, sys
 rep, out, title = sys.argv[1], sys.argv[2], sys.argv[3]
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(raw.splitlines()))
@@ -25,3 +28,13 @@ with open(out, "w") as f:
 r = rows[2]
 g = lambda k: r[hdr.index(k)]
 print(g('Kernel Name')[:70], g('gpu__time_duration.sum'), units[hdr.index('gpu__time_duration.sum')], g('dram__bytes_read.sum'), g('dram__bytes_write.sum'), units[hdr.index('dram__bytes_write.sum')])
+
+if len(sys.argv) > 5:
+    path, key = sys.argv[4], sys.argv[5]
+    scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+    tot = sum(float(g(k)) * scale[units[hdr.index(k)]] for k in ('dram__bytes_read.sum', 'dram__bytes_write.sum'))
+    d = json.load(open(path)) if os.path.exists(path) else {}
+    d[key] = int(tot)
+    d.setdefault("_kernels", {})[key] = g('Kernel Name')
+    d.setdefault("_time_us", {})[key] = float(g('gpu__time_duration.sum')) * {"us": 1, "ms": 1e3, "ns": 1e-3, "s": 1e6}[units[hdr.index('gpu__time_duration.sum')]]
+    json.dump(d, open(path, "w"), indent=1)
