@@ -12,6 +12,7 @@ cap() {   # name  kernel-regex  skip  title  command...
   local name=$1 kre=$2 skip=$3 title=$4; shift 4
   timeout 600 ncu --set full --clock-control none --import-source on -k regex:$kre -s $skip -c 1 -f -o $O/r02_ncu_$name "$@" > $O/r02_ncu_$name.log 2>&1
   python tools/ncu_summary.py $O/r02_ncu_$name.ncu-rep $O/r02_ncu_$name.md "ncu --set full --clock-control none: $title (source $REV, library sha256 $SO)" $O/r02_traffic.json $name
+  [ "$name" = c3 ] || rm -f $O/r02_ncu_$name.ncu-rep      # gpurun brings back at most 64 MiB: the summaries travel, one report stays
 }
 cap c3      rows_reg    1 "C3 1,048,576 x 4096 -> 1024 float32"            python tools/one_shape.py 1048576 4096 1024 f32
 cap c2      rows_reg    1 "C2 65,536 x 768 -> 256 float32"                 python tools/one_shape.py 65536 768 256 f32
