@@ -68,7 +68,8 @@ void run_reg(const Shape& s, const void* in, void* out, Timer& tm, int waves = 1
 // Request-sized launches (C2: 65,536 x 768 -> 256 f32, 128 MiB per launch): rotate over NSET
 // buffer pairs so nothing is served from L2, launch with programmatic dependent launch.
 template <typename T, int VB, int NV, int R, int MODE, int MINB, int L>
-void run_reg_small(const char* label, int64_t rows, int64_t D, int64_t k, int es, Timer& tm, bool pdl, int threads = kThreads) {
+void run_reg_small(const char* label, int64_t rows, int64_t D, int64_t k, int es, Timer& tm, bool pdl, int threads = kThreads,
+                   int waves = 0) {
   constexpr int NSET = 6;
   static void* in[NSET]; static void* out[NSET]; static int64_t have = 0;
   if (have != rows * D) {
@@ -81,7 +82,12 @@ void run_reg_small(const char* label, int64_t rows, int64_t D, int64_t k, int es
   }
   auto kern = rows_reg_kernel<T, VB, NV, R, L, MODE, MINB, 1>;
   const int64_t rpb = (threads / 32) * R * (32 / L);
-  const int grid = (int)((rows + rpb - 1) / rpb);
+  int grid = (int)((rows + rpb - 1) / rpb);
+  if (waves > 0) {                                      // persistent: whole waves of resident blocks, grid-stride loop
+    int per_sm = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, 0));
+    grid = std::min(grid, g_sms * per_sm * waves);
+  }
   const int nvec = (int)(k * es / VB);
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid); cfg.blockDim = dim3(threads);
@@ -385,6 +391,12 @@ int main(int argc, char** argv) {
       run_reg_small<float, 32, 1, 4, 1, 4, 32>("C2 64Kx768->256", 65536, 768, 256, 4, tm, pdl, 128);
       run_reg_small<float, 32, 1, 4, 1, 4, 32>("C2 64Kx768->256", 65536, 768, 256, 4, tm, pdl, 64);
       run_reg_small<float, 16, 2, 4, 1, 4, 32>("C2 64Kx768->256", 65536, 768, 256, 4, tm, pdl);
+      // whole waves of resident blocks, rows dealt grid-stride (finer quanta with fewer rows per warp)
+      run_reg_small<float, 32, 1, 1, 1, 8, 32>("C2 persistent", 65536, 768, 256, 4, tm, pdl, kThreads, 1);
+      run_reg_small<float, 32, 1, 2, 1, 6, 32>("C2 persistent", 65536, 768, 256, 4, tm, pdl, kThreads, 1);
+      run_reg_small<float, 32, 1, 4, 1, 4, 32>("C2 persistent", 65536, 768, 256, 4, tm, pdl, kThreads, 1);
+      run_reg_small<float, 32, 1, 1, 1, 8, 32>("C2 one-shot R=1", 65536, 768, 256, 4, tm, pdl);
+      run_reg_small<float, 32, 1, 2, 1, 8, 32>("C2 one-shot R=2 minb8", 65536, 768, 256, 4, tm, pdl);
     }
     return 0;
   }
