@@ -239,6 +239,82 @@ void b64_encode(const unsigned char* src, size_t nbytes, char* dst) {
   }
 }
 
+// ---- fast path for the common embedding array: nothing but numbers.
+// A table-driven automaton walks the bytes (one dependent table load per byte, no branches on
+// digits), counts the commas and notes where the dims-th element ends.  Anything that is not a
+// plain array of numbers (a string, a nested value, a syntax error) makes it give up, and the
+// general scanner below redoes the array from its '['.  Tokens that could overflow float64 — the
+// ones with an exponent or more than 300 characters — are handed to skip_number for the exact check.
+enum : uint8_t { C_D0, C_D19, C_MINUS, C_PLUS, C_DOT, C_WS, C_E, C_COMMA, C_CLOSE, C_OTHER, C_COUNT };
+enum : uint8_t { S_START, S_MINUS, S_ZERO, S_INT, S_DOT, S_FRAC, S_EXP, S_EXPSIGN, S_EXPDIG, S_AFTER, S_DONE, S_ERR, S_COUNT };
+struct NumberArrayDfa {
+  uint8_t cls[256];
+  uint8_t next[S_COUNT][C_COUNT];
+  NumberArrayDfa() {
+    memset(cls, C_OTHER, sizeof cls);
+    cls[(unsigned char)'0'] = C_D0;
+    for (int c = '1'; c <= '9'; ++c) cls[c] = C_D19;
+    cls[(unsigned char)'-'] = C_MINUS; cls[(unsigned char)'+'] = C_PLUS; cls[(unsigned char)'.'] = C_DOT;
+    cls[(unsigned char)' '] = cls[(unsigned char)'\t'] = cls[(unsigned char)'\n'] = cls[(unsigned char)'\r'] = C_WS;
+    cls[(unsigned char)'e'] = cls[(unsigned char)'E'] = C_E;
+    cls[(unsigned char)','] = C_COMMA; cls[(unsigned char)']'] = C_CLOSE;
+    memset(next, S_ERR, sizeof next);
+    auto ends = [&](int st) { next[st][C_WS] = S_AFTER; next[st][C_COMMA] = S_START; next[st][C_CLOSE] = S_DONE; };
+    next[S_START][C_WS] = S_START; next[S_START][C_MINUS] = S_MINUS; next[S_START][C_D0] = S_ZERO; next[S_START][C_D19] = S_INT;
+    next[S_MINUS][C_D0] = S_ZERO; next[S_MINUS][C_D19] = S_INT;
+    next[S_ZERO][C_DOT] = S_DOT; next[S_ZERO][C_E] = S_EXP; ends(S_ZERO);
+    next[S_INT][C_D0] = next[S_INT][C_D19] = S_INT; next[S_INT][C_DOT] = S_DOT; next[S_INT][C_E] = S_EXP; ends(S_INT);
+    next[S_DOT][C_D0] = next[S_DOT][C_D19] = S_FRAC;
+    next[S_FRAC][C_D0] = next[S_FRAC][C_D19] = S_FRAC; next[S_FRAC][C_E] = S_EXP; ends(S_FRAC);
+    next[S_EXP][C_PLUS] = next[S_EXP][C_MINUS] = S_EXPSIGN; next[S_EXP][C_D0] = next[S_EXP][C_D19] = S_EXPDIG;
+    next[S_EXPSIGN][C_D0] = next[S_EXPSIGN][C_D19] = S_EXPDIG;
+    next[S_EXPDIG][C_D0] = next[S_EXPDIG][C_D19] = S_EXPDIG; ends(S_EXPDIG);
+    ends(S_AFTER); next[S_AFTER][C_WS] = S_AFTER;
+  }
+};
+const NumberArrayDfa kDfa;
+
+// sc.p just behind '[' and its white space, the array not empty.  1 = scanned (sc.p behind ']'),
+// 0 = not a plain number array (sc.p untouched: use the general scanner), -1 = a number that
+// overflows float64 (the reference's decode fails).
+int scan_number_array_fast(Scanner& sc, int64_t dims, Span* out) {
+  const char* p = sc.p;
+  const char* const e = sc.e;
+  const char* tok = p;                               // first byte after the last comma (or after '[')
+  unsigned st = S_START;
+  int64_t count = 0;
+  bool has_exp = false;
+  for (; p < e; ++p) {
+    const unsigned c = kDfa.cls[(unsigned char)*p];
+    st = kDfa.next[st][c];
+    if (c < C_E) continue;                           // digits, sign, dot, white space: nothing to note
+    if (c == C_E) { has_exp = true; continue; }
+    if (st == S_ERR) return 0;
+    // a comma or the closing bracket: one more element, which ended somewhere before p
+    if (has_exp || p - tok > 300) {
+      Scanner one{sc.b, p, tok};
+      one.ws();
+      if (!one.skip_number()) return -1;
+      has_exp = false;
+    }
+    ++count;
+    if (count == dims) {
+      const char* q = p;
+      while (q > tok && (q[-1] == ' ' || q[-1] == '\t' || q[-1] == '\n' || q[-1] == '\r')) --q;
+      out->cut = q - sc.b;
+    }
+    if (c == C_CLOSE) {
+      out->count = count;
+      out->numeric = true;
+      sc.p = p + 1;
+      out->close = sc.p - sc.b;
+      return 1;
+    }
+    tok = p + 1;
+  }
+  return 0;                                          // ran off the end: let the general scanner report it
+}
+
 // p at '[' of an embedding array.  Records the span; `dims` bounds the numeric check.
 bool scan_embedding(Scanner& sc, int64_t dims, Span* out) {
   out->open = sc.p - sc.b;
@@ -247,6 +323,12 @@ bool scan_embedding(Scanner& sc, int64_t dims, Span* out) {
   out->numeric = true;
   ++sc.p; sc.ws();
   if (sc.p < sc.e && *sc.p == ']') { ++sc.p; out->close = sc.p - sc.b; return true; }
+  {
+    const int fast = scan_number_array_fast(sc, dims, out);
+    if (fast == 1) return true;
+    if (fast < 0) return sc.fail();
+    out->count = 0; out->cut = -1; out->numeric = true;
+  }
   for (;;) {
     sc.ws();
     if (sc.p >= sc.e) return sc.fail();
@@ -652,16 +734,19 @@ int64_t etn_json_truncate_response(const char* json, size_t len, int64_t dims, i
   parallel_for(host64.size(), 8, [&](size_t g) {
     flen[g] = etn_json_format_array(vals + g * dims, dims, ftext.data() + g * fstride, fstride);
   });
-  // splice
+  // splice: first lay the output out as a list of pieces (what goes where), then let the host
+  // threads copy them — the pieces are independent and a C1-sized answer is 20 MB of them
+  struct Piece { const char* p; size_t n, o; int kind; };   // kind 0: copy, 1: base64 of n raw bytes at p, 2: base64 prefix of a base64 text at p
+  std::vector<Piece> pieces;
+  pieces.reserve(spans.size() * 3 + 1);
   size_t o = 0, src = 0, g64 = 0, g32 = 0;
   auto put = [&](const char* p, size_t n) -> bool {
     if (o + n > out_cap) return false;
-    memcpy(out + o, p, n);
+    if (n) pieces.push_back({p, n, o, 0});
     o += n;
     return true;
   };
   bool fits = true;
-  std::vector<unsigned char> tmp;
   for (size_t i = 0; i < spans.size() && fits; ++i) {
     const Span& s = spans[i];
     if (s.count <= dims) continue;                 // left whole, never padded (handlers.go:2074)
@@ -670,21 +755,17 @@ int64_t etn_json_truncate_response(const char* json, size_t len, int64_t dims, i
     if (s.b64) {
       const size_t nbytes = (size_t)dims * 4, enc = b64_encoded_len(nbytes);
       if (o + enc + 2 > out_cap) { fits = false; break; }
-      const unsigned char* bytes;
+      put("\"", 1);
       if (g32 < gpu32.size() && gpu32[g32] == i) {
-        bytes = (const unsigned char*)(vals32 + g32 * dims);
+        pieces.push_back({(const char*)(vals32 + g32 * dims), nbytes, o, 1});
         ++g32;
         if (stats) ++stats[0];
       } else {
-        tmp.resize(nbytes);
-        b64_decode_prefix(json + s.open + 1, nbytes, tmp.data());
-        bytes = tmp.data();
+        pieces.push_back({json + s.open + 1, nbytes, o, 2});
         if (stats) ++stats[1];
       }
-      out[o++] = '"';
-      b64_encode(bytes, nbytes, out + o);
       o += enc;
-      out[o++] = '"';
+      put("\"", 1);
     } else if (g64 < gpu64.size() && gpu64[g64] == i) {
       const int64_t w = text_on_gpu ? (int64_t)gres.len[g64] : flen[g64];
       if (w < 0) { if (own) etn_free_pinned(own); return w; }     // NaN/Inf: Go's encoder would refuse too
@@ -699,6 +780,21 @@ int64_t etn_json_truncate_response(const char* json, size_t len, int64_t dims, i
     src = (size_t)s.close;
   }
   if (fits) fits = put(json + src, len - src);
+  if (fits) {
+    auto run = [&](const Piece& q) {
+      if (q.kind == 0) { memcpy(out + q.o, q.p, q.n); return; }
+      if (q.kind == 1) { b64_encode((const unsigned char*)q.p, q.n, out + q.o); return; }
+      std::vector<unsigned char> raw(q.n);
+      b64_decode_prefix(q.p, q.n, raw.data());
+      b64_encode(raw.data(), q.n, out + q.o);
+    };
+    // a few large groups of pieces per thread rather than one piece at a time
+    const size_t per = 64;
+    const size_t groups = (pieces.size() + per - 1) / per;
+    parallel_for(groups, o >= (4u << 20) ? 2 : groups + 1, [&](size_t g) {
+      for (size_t i = g * per; i < std::min(pieces.size(), (g + 1) * per); ++i) run(pieces[i]);
+    });
+  }
   if (own) etn_free_pinned(own);
   if (!fits) return ETN_ERR_SHAPE;
   if (stats) stats[2] = (int64_t)spans.size();

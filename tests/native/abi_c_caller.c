@@ -44,6 +44,33 @@ int main(void) {
   CHECK(rc == 0, "truncate: %s", etn_strerror(rc));
   for (int64_t r = 0; r < batch; r += 131) CHECK(memcmp(out + r * k, in + r * D, (size_t)k * 8) == 0, "truncate row %ld", (long)r);
 
+  /* two responses with different `dimensions` in flight at once (tickets), then one ragged call
+   * that carries both: the batcher's view of handlers.go:1874-1877 */
+  {
+    const int64_t n1 = 300, n2 = 200, k1 = 256, k2 = 100;
+    double *o1 = (double *)etn_alloc_pinned((size_t)(n1 * k1) * 8), *o2 = (double *)etn_alloc_pinned((size_t)(n2 * k2) * 8);
+    double *packed = (double *)etn_alloc_pinned((size_t)(n1 * k1 + n2 * k2) * 8);
+    int32_t *kpr = (int32_t *)malloc((size_t)(n1 + n2) * sizeof(int32_t));
+    CHECK(o1 && o2 && packed && kpr, "allocation");
+    int64_t t1 = 0, t2 = 0;
+    rc = etn_submit_host(n1, D, k1, NULL, ETN_F64, ETN_TRUNCATE_RENORM, in, 0, o1, 0, &t1);
+    CHECK(rc == 0 && t1 > 0, "submit 1: %s", etn_strerror(rc));
+    rc = etn_submit_host(n2, D, k2, NULL, ETN_F64, ETN_TRUNCATE_RENORM, in + n1 * D, 0, o2, 0, &t2);
+    CHECK(rc == 0 && t2 > t1, "submit 2: %s", etn_strerror(rc));
+    CHECK(etn_wait(t2) == 0 && etn_wait(t1) == 0, "wait");
+    CHECK(etn_wait(t1) == ETN_ERR_TICKET, "a ticket is waited for once");
+    for (int64_t r = 0; r < n1 + n2; ++r) kpr[r] = r < n1 ? (int32_t)k1 : (int32_t)k2;
+    rc = embed_truncate_norm_ragged_host(n1 + n2, D, kpr, ETN_F64, ETN_TRUNCATE_RENORM, in, 0, packed, 0);
+    CHECK(rc == 0, "ragged host: %s", etn_strerror(rc));
+    CHECK(memcmp(packed, o1, (size_t)(n1 * k1) * 8) == 0, "ragged rows of request 1 differ from its own call");
+    CHECK(memcmp(packed + n1 * k1, o2, (size_t)(n2 * k2) * 8) == 0, "ragged rows of request 2 differ from its own call");
+    int64_t cuts[3];
+    CHECK(etn_shard_ragged(n1 + n2, D, kpr, 2, cuts) == 0 && cuts[0] == 0 && cuts[2] == n1 + n2 && cuts[1] > 0 && cuts[1] < n1, "shard cut %ld", (long)cuts[1]);
+    kpr[5] = 0;
+    CHECK(embed_truncate_norm_ragged_host(n1 + n2, D, kpr, ETN_F64, ETN_TRUNCATE_RENORM, in, 0, packed, 0) == ETN_ERR_SHAPE, "k <= 0 must be refused");
+    etn_free_pinned(o1); etn_free_pinned(o2); etn_free_pinned(packed); free(kpr);
+  }
+
   /* the JSON packer, the way proxyOpenAIEmbed would hand it a provider body */
   const char body[] = "{\"object\":\"list\",\"data\":[{\"index\":0,\"embedding\":[3,4,0,0]},{\"index\":1,\"embedding\":[1,2]}],\"usage\":{\"prompt_tokens\":2}}";
   char rewritten[256];
@@ -57,13 +84,14 @@ int main(void) {
   int64_t ctr[ETN_CTR_COUNT];
   CHECK(etn_get_counters(ctr, ETN_CTR_COUNT) == ETN_CTR_COUNT, "counters");
   /* host calls: the static probe, two C1 calls, the packer's one vector; the refused call before etn_init is a fallback, not an error */
-  CHECK(ctr[ETN_CTR_HOST_CALLS] == 4 && ctr[ETN_CTR_HOST_ROWS] == 2 * batch + 2 && ctr[ETN_CTR_ERRORS] == 0 && ctr[ETN_CTR_FALLBACKS] == 1,
+  /* + two tickets (300 + 200 rows) and one ragged call (500 rows); its refused twin (k <= 0) is an argument error */
+  CHECK(ctr[ETN_CTR_HOST_CALLS] == 7 && ctr[ETN_CTR_HOST_ROWS] == 2 * batch + 2 + 1000 && ctr[ETN_CTR_ERRORS] == 1 && ctr[ETN_CTR_FALLBACKS] == 1,
         "counter values %ld %ld %ld %ld", (long)ctr[ETN_CTR_HOST_CALLS], (long)ctr[ETN_CTR_HOST_ROWS], (long)ctr[ETN_CTR_ERRORS],
         (long)ctr[ETN_CTR_FALLBACKS]);
   double le[32], hsum = 0;
   int64_t hc[32];
   int nb = etn_get_histogram(ETN_HIST_BATCH_ROWS, le, hc, 32, &hsum);
-  CHECK(nb > 2 && hsum == (double)(2 * batch + 2), "batch-rows histogram: %d buckets, sum %g", nb, hsum);
+  CHECK(nb > 2 && hsum == (double)(2 * batch + 2 + 1000), "batch-rows histogram: %d buckets, sum %g", nb, hsum);
   CHECK(strcmp(etn_counter_name(ETN_CTR_KERNEL_LAUNCHES), "llmcore_embed_gpu_kernel_launches_total") == 0, "counter name");
 
   etn_free_pinned(in);
