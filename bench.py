@@ -266,6 +266,10 @@ def quick_measure(torch, eg, wl, peak, steps=100, warmup=5):
     torch.cuda.synchronize()
     s_per = ev0.elapsed_time(ev1) * 1e-3 / steps
     gbs = per_set / s_per / 1e9
+    # the timed output is a real result: unit rows at both ends of the batch
+    for sl in (slice(0, 2048), slice(rows - 2048, rows)):
+        nrm = torch.linalg.vector_norm(ys[0][sl].double(), dim=1)
+        assert float((nrm - 1).abs().max()) < (2e-6 if es == 4 else 1e-13), f"{wl['desc']}: output rows are not unit-norm"
     return {"workload": wl["desc"], "vectors_per_s": rows / s_per, "us_per_launch": s_per * 1e6, "achieved_GBps": gbs,
             "frac_of_measured_peak": gbs / peak, "buffer_sets": n_sets, "steps": steps}
 
@@ -326,6 +330,9 @@ def ragged_measure(torch, eg, peak, rows=1048576, D=4096, steps=50):
     torch.cuda.synchronize()
     t = e0.elapsed_time(e1) * 1e-3 / steps
     gbs = 2 * 8 * int(off[-1]) / t / 1e9
+    for r in (0, rows // 2, rows - 1):                           # packed rows of the timed output are unit vectors
+        v = out[int(off[r]):int(off[r + 1])]
+        assert abs(float(torch.linalg.vector_norm(v)) - 1.0) < 1e-13 and v.numel() == int(kpr[r]), "C5 output is not unit-norm"
     return {"workload": "ragged mixed-request batch, %d rows x %d float64, per-request k in {64,128,256,512,1024}, mean k %.1f" % (rows, D, kpr.mean()),
             "vectors_per_s": rows / t, "us_per_launch": t * 1e6, "achieved_GBps": gbs, "frac_of_measured_peak": gbs / peak,
             "kernel": "etn::rows_ring_kernel<double> (page-granular bulk-async ring)", "steps": steps}
