@@ -261,3 +261,70 @@ def test_histogram_counts_add_up_to_the_counters(oracle):
     ksum = h1[1]["sum"] - h0[1]["sum"]
     assert 0 < ksum < 0.05                                       # seconds of kernel time, from CUDA events
     assert "llmcore_embed_gpu_kernel_seconds_bucket" in eg.metrics_text()
+
+
+# ---------------------------------------------------------------- stress, lifetime ----
+def test_mixed_traffic_from_many_threads(oracle):
+    """Sixteen handler threads for a few seconds, each issuing its own mix of dense calls, ragged
+    calls, tickets and plain truncation with its own shapes, while the workers merge, split and
+    pipeline whatever is queued.  Every caller must get exactly its own rows back."""
+    import time
+    rng0 = np.random.default_rng(2026)
+    shapes = [(int(rng0.integers(1, 3000)), int(rng0.choice([768, 1024, 1536, 4096])), int(rng0.choice([64, 100, 256, 257, 1024, 5000])),
+               rng0.choice([np.float32, np.float64])) for _ in range(16)]
+    inputs = [oracle.fill(300 + t, r, D, dt) for t, (r, D, k, dt) in enumerate(shapes)]
+    wants = [oracle.renorm_exact(x, k) for x, (_, _, k, _) in zip(inputs, shapes)]
+    kprs = [np.random.default_rng(t).integers(1, D + 50, size=r).astype(np.int32) for t, (r, D, _, _) in enumerate(shapes)]
+    rag_wants = [oracle.ragged(x, kp, eg.TRUNCATE_RENORM)[0] for x, kp in zip(inputs, kprs)]
+    errs, calls = [], [0] * 16
+    deadline = time.time() + 3.0
+
+    def handler(t):
+        x, (_, D, k, _) = inputs[t], shapes[t]
+        try:
+            i = 0
+            while time.time() < deadline:
+                kind = (i + t) % 4
+                if kind == 0:
+                    _ulp(oracle, eg.truncate_norm_host(x, k), wants[t])
+                elif kind == 1:
+                    _ulp(oracle, eg.truncate_norm_ragged_host(x, kprs[t]), rag_wants[t])
+                elif kind == 2:
+                    tk = [eg.Ticket(x, k) for _ in range(3)]
+                    for q in tk:
+                        _ulp(oracle, q.wait(), wants[t])
+                else:
+                    assert np.array_equal(eg.truncate_norm_host(x, k, eg.TRUNCATE), x[:, :min(k, D)])
+                i += 1
+            calls[t] = i
+        except Exception as e:  # noqa: BLE001
+            errs.append((t, shapes[t], repr(e)[:300]))
+
+    th = [threading.Thread(target=handler, args=(t,)) for t in range(16)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not errs, errs
+    assert min(calls) >= 2, calls
+
+
+def test_init_shutdown_cycles_give_the_memory_back(oracle):
+    """etn_init takes 4 x (64 + 64) MiB per device; etn_shutdown has to return all of it, every
+    time, whether or not calls were made in between."""
+    x = oracle.fill(4, 2000, 1024, np.float32)
+    want = oracle.renorm_exact(x, 256)
+    eg.shutdown()
+    torch.cuda.set_device(0)
+    torch.cuda.synchronize()
+    _ulp(oracle, (eg.init([0]), eg.truncate_norm_host(x, 256))[1], want)       # first cycle loads the kernels
+    eg.shutdown()
+    free0, _ = torch.cuda.mem_get_info()
+    for cycle in range(4):
+        assert eg.init([0]) == 1
+        during, _ = torch.cuda.mem_get_info()
+        assert free0 - during >= 4 * 128 * (1 << 20)
+        if cycle % 2 == 0:
+            _ulp(oracle, eg.truncate_norm_host(x, 256), want)
+        eg.shutdown()
+        after, _ = torch.cuda.mem_get_info()
+        assert after >= free0 - (8 << 20), (cycle, free0, after)
+    assert eg.init() >= 1
