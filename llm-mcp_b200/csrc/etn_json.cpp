@@ -741,6 +741,11 @@ int64_t etn_json_truncate_response(const char* json, size_t len, int64_t dims, i
   if (own) etn_free_pinned(own);
   if (!fits) return ETN_ERR_SHAPE;
   if (stats) stats[2] = (int64_t)spans.size();
+  if (mode == ETN_TRUNCATE_RENORM) {                 // renormalisation was asked for and these vectors only got the cut
+    int64_t only_cut = 0;
+    for (size_t i = 0; i < spans.size(); ++i) only_cut += spans[i].count > dims && !spans[i].numeric;
+    if (only_cut) etn_note_fallback(only_cut);
+  }
   return (int64_t)o;
 }
 

@@ -18,6 +18,7 @@ void json_gpu_release(JsonGpuResult*) {}
 extern "C" {
 void* etn_alloc_pinned(size_t n) { return malloc(n); }
 void etn_free_pinned(void* p) { free(p); }
+void etn_note_fallback(int64_t) {}
 int embed_truncate_norm_host(int64_t batch, int64_t, int64_t k, int dtype, int, const void* in, int64_t, void* out, int) {
   if (in != out) memcpy(out, in, (size_t)(batch * k) * (dtype == ETN_F32 ? 4 : 8));
   return 0;   // identity "renorm": enough to drive the parse -> format path

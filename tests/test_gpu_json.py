@@ -146,3 +146,40 @@ def test_numbers_the_fast_parser_declines_are_redone_by_the_host(oracle):
     os.environ.pop("ETN_JSON_GPU")
     assert dev == host
     assert json.loads(dev) == json.loads(host)
+
+
+@pytest.mark.parametrize("dims,n_src", [(1, 5), (3, 7), (255, 300), (4096, 4100), (7000, 7001)])
+def test_device_path_at_the_ends_of_its_range(oracle, dims, n_src):
+    """One kept number per vector, thousands of them, and the largest prefix whose text still
+    fits a block's shared memory (7,000 numbers; beyond that the host path takes over): the
+    answer is the host path's, byte for byte."""
+    rng = np.random.default_rng(dims)
+    x = [list(map(float, rng.standard_normal(n_src) * 0.05)) for _ in range(5)]
+    x[2] = x[2][:dims]                                           # exactly dims long: left whole
+    body = _body(x, ("\n , ", ": "))
+    os.environ["ETN_JSON_GPU"] = "0"
+    host, hs = eg.truncate_response_json(body, dims, renorm=True)
+    os.environ["ETN_JSON_GPU"] = "1"
+    l0 = eg.counters()["llmcore_embed_gpu_kernel_launches_total"]
+    dev, ds = eg.truncate_response_json(body, dims, renorm=True)
+    launches = eg.counters()["llmcore_embed_gpu_kernel_launches_total"] - l0
+    os.environ.pop("ETN_JSON_GPU")
+    assert dev == host and ds == hs == {"gpu_vectors": 4, "resliced_vectors": 0, "arrays": 5}
+    assert launches == 3, launches                               # parse, renormalise, format: it did run on the device
+    got = json.loads(dev)["data"]
+    assert [len(d["embedding"]) for d in got] == [dims] * 5
+    for d, v in zip(got, x):
+        want = oracle.renorm_exact(np.array([v]), dims)[0] if len(v) > dims else np.array(v)
+        dd, i = oracle.max_ulp(np.array(d["embedding"], dtype=np.float64), want)
+        assert 0 <= dd <= 2, (dd, i)
+
+
+def test_vectors_that_only_get_the_cut_are_counted_as_fallbacks(oracle):
+    x = [list(map(float, r)) for r in oracle.fill(3, 4, 64, np.float64)]
+    x[1][3] = "not a number"                                     # cannot be renormalised: the reference reslice, on the text
+    body = _body(x)
+    f0 = eg.counters()["llmcore_embed_gpu_fallback_total"]
+    out, st = eg.truncate_response_json(body, 16, renorm=True)
+    assert st == {"gpu_vectors": 3, "resliced_vectors": 1, "arrays": 4}
+    assert json.loads(out)["data"][1]["embedding"] == x[1][:16]
+    assert eg.counters()["llmcore_embed_gpu_fallback_total"] == f0 + 1

@@ -16,6 +16,7 @@ void json_gpu_release(JsonGpuResult*) {}
 extern "C" {
 void* etn_alloc_pinned(size_t n) { return malloc(n); }
 void etn_free_pinned(void* p) { free(p); }
+void etn_note_fallback(int64_t) {}
 int embed_truncate_norm_host(int64_t, int64_t, int64_t, int, int, const void*, int64_t, void*, int) { return 0; }
 }
 
