@@ -9,6 +9,7 @@ golden vectors for this path.
 from __future__ import annotations
 
 import ctypes
+import json
 import os
 import subprocess
 
@@ -318,3 +319,50 @@ def b64_vector_ref(text: str, dims: int, renorm: bool):
     if renorm:
         v = renorm_exact(v[None, :], dims)[0]
     return base64.b64encode(v.astype("<f4").tobytes()).decode()
+
+
+# ---------------------------------------------------------------------------
+# Handler-level restatement (pure Python): the cloud branch of HandleEmbeddings
+# ---------------------------------------------------------------------------
+
+def handle_embeddings_ref(request: dict, env: dict, provider):
+    """core/internal/api/handlers.go:1821-1896 + proxyOpenAIEmbed :2018-2060 on an already decoded,
+    well-formed request dict {"model", "input", "dimensions"?}: what the reference forwards to the
+    provider and what it answers.  `provider(forwarded: dict) -> (status, body bytes)`.
+    Returns (status, decoded JSON value of the response body, forwarded dict or None).
+    Test infrastructure: the checker for llm-mcp_b200/handler.py."""
+    model, inp = request.get("model", ""), request.get("input")
+    def err(status, code, message):
+        return status, {"error": code, "message": message}, None
+    if model == "":
+        return err(400, "model_required", "Field 'model' is required")
+    if isinstance(inp, str):
+        texts = [inp]
+    elif isinstance(inp, list):
+        texts = [t for t in inp if isinstance(t, str)]                  # :1849-1853: other items silently dropped
+    else:
+        return err(400, "invalid_input", "Field 'input' must be a string or array of strings")
+    if not texts:
+        return err(400, "empty_input", "Input is empty")
+    if "/" not in model:
+        raise ValueError("local branch: not restated here")
+    key = env.get("OPENROUTER_API_KEY", "")
+    if key in ("", "not-used"):
+        return err(503, "no_api_key", "OPENROUTER_API_KEY not configured")
+    dims = resolve_dims(int(request.get("dimensions", 0) or 0), env)    # :1874-1877
+    forwarded = {"model": model, "input": texts}
+    if dims > 0:                                                        # :2023-2025
+        forwarded["dimensions"] = dims
+    status, body = provider(forwarded)
+    if status != 200:                                                   # :2042-2045
+        msg = "cloud embed returned %d: %s" % (status, body[:1024].decode("utf-8", errors="replace"))
+        return 502, {"error": "cloud_embed_failed", "message": msg}, forwarded
+    try:
+        result = json.loads(body)                                       # :2047-2050
+        if result is not None and not isinstance(result, dict):
+            raise ValueError("not an object")
+    except ValueError:
+        return 502, {"error": "cloud_embed_failed", "message": "decode cloud embed response: ..."}, forwarded
+    if dims > 0 and result is not None:                                 # :1891-1893
+        truncate_embeddings_ref(result, dims)
+    return 200, result, forwarded

@@ -183,3 +183,22 @@ def test_vectors_that_only_get_the_cut_are_counted_as_fallbacks(oracle):
     assert st == {"gpu_vectors": 3, "resliced_vectors": 1, "arrays": 4}
     assert json.loads(out)["data"][1]["embedding"] == x[1][:16]
     assert eg.counters()["llmcore_embed_gpu_fallback_total"] == f0 + 1
+
+
+def test_handler_with_renormalisation_on(oracle):
+    """POST /v1/embeddings, cloud branch, EMBED_RENORMALIZE=1: the provider ignores `dimensions`,
+    the handler mirror cuts and renormalises through the packer's device path."""
+    from llm_mcp_b200 import handler as h
+    x = oracle.fill(6, 5, 512, np.float64)
+    body = json.dumps({"object": "list", "data": [{"index": i, "embedding": r.tolist()} for i, r in enumerate(x)],
+                       "usage": {"prompt_tokens": 12}}).encode()
+    env = {"OPENROUTER_API_KEY": "k", "EMBED_RENORMALIZE": "1", "CLOUD_EMBED_DIMENSIONS": "128"}
+    m = h.Metrics()
+    status, _, out = h.handle_embeddings("POST", b'{"model":"qwen/qwen3-embedding-8b","input":["a","b","c","d","e"]}', env, lambda u, hd, b: (200, body), m)
+    assert status == 200 and m.input_tokens == {("qwen/qwen3-embedding-8b", "openrouter"): 12.0}
+    got = json.loads(out)
+    assert [d["index"] for d in got["data"]] == list(range(5)) and got["usage"] == {"prompt_tokens": 12}
+    want = oracle.renorm_exact(x, 128)
+    for d, w in zip(got["data"], want):
+        dd, i = oracle.max_ulp(np.array(d["embedding"], dtype=np.float64), w)
+        assert 0 <= dd <= 2, (dd, i)
