@@ -28,8 +28,11 @@
 #include <atomic>
 #include <charconv>
 #include <cmath>
+#include <condition_variable>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
+#include <pthread.h>
 #include <string.h>
 #include <mutex>
 #include <string>
@@ -291,11 +294,81 @@ bool scan_embedding(Scanner& sc, int64_t dims, Span* out) {
 
 // Vectors are independent, so number parsing and formatting spread over host threads
 // (handlers run one goroutine per connection; a large response still deserves the cores).
+// Host threads for the packer.  Creating and joining sixteen threads costs a few hundred
+// microseconds, three times per response — a tenth of a C1-sized call — so the threads are kept:
+// a small pool, created on first use and never torn down (its threads sleep on a condition
+// variable).  One parallel region at a time; a caller that finds the pool taken (another handler
+// is in its own region) spawns threads of its own as before.  Items are handed out one at a
+// time from an atomic counter, so uneven items balance themselves.
+std::atomic<bool> g_pool_lost{false};                // set in the child of a fork(): the pool's threads did not come along
+
+class Pool {
+ public:
+  static Pool& get() { static Pool* p = new Pool(); return *p; }      // leaked on purpose: no join at exit
+  size_t size() const { return workers_ + 1; }
+  template <typename F>
+  bool run(size_t n, size_t threads, F& f) {
+    if (g_pool_lost.load(std::memory_order_relaxed)) return false;
+    std::unique_lock<std::mutex> region(region_, std::try_to_lock);
+    if (!region.owns_lock()) return false;
+    const size_t helpers = std::min(workers_, threads > 0 ? threads - 1 : 0);
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      fn_ = [&f](size_t i) { f(i); };
+      n_ = n;
+      next_.store(0, std::memory_order_relaxed);
+      wanted_ = helpers;
+      active_ = helpers;
+      ++gen_;
+    }
+    if (helpers == workers_) cv_.notify_all(); else for (size_t i = 0; i < helpers; ++i) cv_.notify_one();
+    for (size_t i; (i = next_.fetch_add(1, std::memory_order_relaxed)) < n;) f(i);
+    std::unique_lock<std::mutex> lk(mu_);
+    done_.wait(lk, [&] { return active_ == 0; });
+    fn_ = nullptr;
+    return true;
+  }
+
+ private:
+  Pool() {
+    const size_t hw = std::max<size_t>(1, std::min<size_t>(std::thread::hardware_concurrency(), 16));
+    workers_ = hw - 1;
+    pthread_atfork(nullptr, nullptr, [] { g_pool_lost.store(true); });
+    for (size_t t = 0; t < workers_; ++t) std::thread([this] { loop(); }).detach();
+  }
+  void loop() {
+    uint64_t seen = 0;
+    for (;;) {
+      std::function<void(size_t)> fn;
+      size_t n;
+      {
+        std::unique_lock<std::mutex> lk(mu_);
+        cv_.wait(lk, [&] { return gen_ != seen && wanted_ > 0; });
+        seen = gen_;
+        --wanted_;
+        fn = fn_;
+        n = n_;
+      }
+      for (size_t i; (i = next_.fetch_add(1, std::memory_order_relaxed)) < n;) fn(i);
+      std::lock_guard<std::mutex> lk(mu_);
+      if (--active_ == 0) done_.notify_all();
+    }
+  }
+  std::mutex region_, mu_;
+  std::condition_variable cv_, done_;
+  std::function<void(size_t)> fn_;
+  std::atomic<size_t> next_{0};
+  size_t n_ = 0, workers_ = 0, wanted_ = 0, active_ = 0;
+  uint64_t gen_ = 0;
+};
+
+// f(i) for i in [0, n) on up to min(16, cores, n / grain) threads.
 template <typename F>
 void parallel_for(size_t n, size_t grain, F f) {
-  size_t nt = std::min<size_t>(std::min<size_t>(std::thread::hardware_concurrency(), 16), n / grain);
+  size_t nt = std::min<size_t>(std::min<size_t>(std::thread::hardware_concurrency(), 16), n / std::max<size_t>(grain, 1));
   if (nt <= 1) { for (size_t i = 0; i < n; ++i) f(i); return; }
-  std::vector<std::thread> th;
+  if (Pool::get().run(n, nt, f)) return;
+  std::vector<std::thread> th;                       // the pool is taken: threads of this call's own
   for (size_t t = 0; t < nt; ++t)
     th.emplace_back([=] { for (size_t i = t; i < n; i += nt) f(i); });
   for (auto& x : th) x.join();
@@ -321,38 +394,35 @@ bool scan_embedding(Scanner& sc, int64_t dims, Span* out);
 void prescan(const char* json, size_t len, int64_t dims, PreScan* ps) {
   const size_t kMin = 4u << 20;                     // not worth threads below 4 MiB
   if (len < kMin) return;
-  const size_t nt = std::min<size_t>(std::min<size_t>(std::thread::hardware_concurrency(), 16), len / (kMin / 4));
-  if (nt <= 1) return;
+  const size_t nthreads = std::min<size_t>(std::min<size_t>(std::thread::hardware_concurrency(), 16), len / (kMin / 4));
+  if (nthreads <= 1) return;
+  const size_t nt = nthreads * 4;                   // four slices per thread, handed out as threads come free
   std::vector<std::vector<Span>> found(nt);
-  std::vector<std::thread> th;
   const size_t chunk = (len + nt - 1) / nt;
   static const char key[] = "\"embedding\"";
   const size_t klen = sizeof key - 1;
-  for (size_t t = 0; t < nt; ++t) {
-    th.emplace_back([&, t] {
-      const char* p = json + t * chunk;
-      const char* stop = json + std::min(len, (t + 1) * chunk);
-      const char* end = json + len;
-      while (p < stop) {
-        const char* q = (const char*)memmem(p, (size_t)(end - p) < (size_t)(stop - p) + klen ? (size_t)(end - p) : (size_t)(stop - p) + klen,
-                                           key, klen);
-        if (!q || q >= stop) break;
-        const char* r = q + klen;
+  parallel_for(nt, 4, [&](size_t t) {
+    const char* p = json + t * chunk;
+    const char* stop = json + std::min(len, (t + 1) * chunk);
+    const char* end = json + len;
+    while (p < stop) {
+      const char* q = (const char*)memmem(p, (size_t)(end - p) < (size_t)(stop - p) + klen ? (size_t)(end - p) : (size_t)(stop - p) + klen,
+                                         key, klen);
+      if (!q || q >= stop) break;
+      const char* r = q + klen;
+      while (r < end && (*r == ' ' || *r == '\t' || *r == '\n' || *r == '\r')) ++r;
+      if (r < end && *r == ':') {
+        ++r;
         while (r < end && (*r == ' ' || *r == '\t' || *r == '\n' || *r == '\r')) ++r;
-        if (r < end && *r == ':') {
-          ++r;
-          while (r < end && (*r == ' ' || *r == '\t' || *r == '\n' || *r == '\r')) ++r;
-          if (r < end && *r == '[') {
-            Scanner sc{json, end, r};
-            Span s;
-            if (scan_embedding(sc, dims, &s)) { found[t].push_back(s); p = sc.p; continue; }
-          }
+        if (r < end && *r == '[') {
+          Scanner sc{json, end, r};
+          Span s;
+          if (scan_embedding(sc, dims, &s)) { found[t].push_back(s); p = sc.p; continue; }
         }
-        p = q + klen;
       }
-    });
-  }
-  for (auto& x : th) x.join();
+      p = q + klen;
+    }
+  });
   for (auto& v : found) ps->spans.insert(ps->spans.end(), v.begin(), v.end());
   std::sort(ps->spans.begin(), ps->spans.end(), [](const Span& a, const Span& b) { return a.open < b.open; });
 }
