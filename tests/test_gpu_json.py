@@ -202,3 +202,46 @@ def test_handler_with_renormalisation_on(oracle):
     for d, w in zip(got["data"], want):
         dd, i = oracle.max_ulp(np.array(d["embedding"], dtype=np.float64), w)
         assert 0 <= dd <= 2, (dd, i)
+
+
+def test_fuzz_device_path_equals_host_path():
+    """Random responses — vector counts and lengths, white space, number spellings (integers,
+    exponents, 20-digit mantissas, negative zero, tiny and huge magnitudes), vectors that cannot
+    be renormalised — through the device path and the host path: same bytes, same statistics."""
+    rng = np.random.default_rng(424242)
+
+    def spell(v):
+        c = rng.integers(0, 8)
+        if c == 0: return repr(float(v))
+        if c == 1: return "%.17g" % v
+        if c == 2: return "%.*e" % (int(rng.integers(0, 18)), v)
+        if c == 3: return str(int(v * 1000))
+        if c == 4: return "%.20f" % v
+        if c == 5: return ("%.6E" % v).replace("E", "e" if rng.integers(0, 2) else "E")
+        if c == 6: return "-0.0" if rng.integers(0, 2) else "0"
+        return repr(float(v) * 10.0 ** int(rng.integers(-200, 200)))
+
+    for trial in range(60):
+        dims = int(rng.choice([1, 2, 7, 64, 300]))
+        seps = [",", ", ", " ,", "\n,\t", " , "]
+        items = []
+        for i in range(int(rng.integers(1, 9))):
+            n = int(rng.integers(max(1, dims - 2), dims + 40))
+            toks = [spell(x) for x in rng.standard_normal(n) * 0.05]
+            if rng.integers(0, 6) == 0 and n > 1:
+                toks[int(rng.integers(0, min(n, dims)))] = '"x"'          # not renormalisable: cut as text
+            sep = str(rng.choice(seps))
+            items.append('{"index": %d, "embedding": [%s%s]}' % (i, " " * int(rng.integers(0, 3)), sep.join(toks)))
+        body = ('{"object": "list", "data": [' + ", ".join(items) + '], "usage": {"prompt_tokens": %d}}' % trial).encode()
+        os.environ["ETN_JSON_GPU"] = "0"
+        try:
+            host = eg.truncate_response_json(body, dims, renorm=True)
+        except eg.EtnError as e:
+            host = ("error", e.code)
+        os.environ["ETN_JSON_GPU"] = "1"
+        try:
+            dev = eg.truncate_response_json(body, dims, renorm=True)
+        except eg.EtnError as e:
+            dev = ("error", e.code)
+        os.environ.pop("ETN_JSON_GPU")
+        assert dev == host, (trial, dims, body[:300])
